@@ -1,0 +1,655 @@
+// dronerl_b200: kernels + C ABI (include/dronerl_b200.h) of the batched DroneRL env for sm_100a.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -shared -Xcompiler -fPIC
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <new>
+
+#include "../../include/dronerl_b200.h"
+#include "env_kernels.cuh"
+
+using namespace drl;
+
+// =================================================================================================
+// kernels
+// =================================================================================================
+
+struct EnvInputs {   // per-env inputs, prefetched one env ahead in warp mode
+    uint4 gv;
+    uint32_t rec, k0, k1;
+    int act;
+};
+
+__device__ __forceinline__ void flush_stats(const Stats& st, unsigned env_steps, unsigned long long* stats, int lane) {
+    const unsigned d = __reduce_add_sync(FULL, st.dones), c = __reduce_add_sync(FULL, st.crashes),
+                   p = __reduce_add_sync(FULL, st.pickups), v = __reduce_add_sync(FULL, st.deliveries),
+                   g = __reduce_add_sync(FULL, st.charging), r = __reduce_add_sync(FULL, st.respawn_pickups);
+    if (lane == 0) {
+        if (env_steps) atomicAdd(stats + DRL_STAT_ENV_STEPS, (unsigned long long)env_steps);
+        if (d) atomicAdd(stats + DRL_STAT_DONES, (unsigned long long)d);
+        if (c) atomicAdd(stats + DRL_STAT_CRASHES, (unsigned long long)c);
+        if (p) atomicAdd(stats + DRL_STAT_PICKUPS, (unsigned long long)p);
+        if (v) atomicAdd(stats + DRL_STAT_DELIVERIES, (unsigned long long)v);
+        if (g) atomicAdd(stats + DRL_STAT_CHARGING, (unsigned long long)g);
+        if (r) atomicAdd(stats + DRL_STAT_RESPAWN_PICKUPS, (unsigned long long)r);
+    }
+}
+
+__device__ __forceinline__ void zero_code(const DevCfg& c, const Smem& sm, int tid, int nthreads) {
+    uint32_t* w = reinterpret_cast<uint32_t*>(sm.code);
+    const int words = (c.off_sdr - c.off_code) >> 2;
+    for (int i = tid; i < words; i += nthreads) w[i] = 0u;
+}
+
+// ---- warp-per-env kernels (grids up to 128 cells) ---------------------------------------------
+
+template <int NB>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+k_step_warp(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint32_t* __restrict__ drones,
+            const uint32_t* __restrict__ keys, const int8_t* __restrict__ actions, float* __restrict__ rewards,
+            uint8_t* __restrict__ dones, float* __restrict__ obs, unsigned long long* __restrict__ stats) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    unsigned char* base = smem_raw + (size_t)warp * c.group_bytes;
+    const Smem sm = carve(base, c);
+    float* tile = reinterpret_cast<float*>(base + c.off_tile);
+    Group<32> grp{nullptr};
+    zero_code(c, sm, lane, 32);
+    const int nvec = c.GS >> 4, n = c.n;
+    const long long stride = (long long)gridDim.x * kWarpsPerBlock;
+    long long e = (long long)blockIdx.x * kWarpsPerBlock + warp;
+    Stats st;
+    unsigned env_steps = 0;
+
+    EnvInputs nxt = {};
+    auto prefetch = [&](long long ee) {
+        if (ee < c.N) {
+            if (lane < nvec) nxt.gv = reinterpret_cast<const uint4*>(ground + ee * c.GS)[lane];
+            if (lane < n) {
+                nxt.rec = drones[ee * n + lane];
+                nxt.act = actions[ee * n + lane];
+            }
+            const uint2 kk = *reinterpret_cast<const uint2*>(keys + 2 * ee);
+            nxt.k0 = kk.x;
+            nxt.k1 = kk.y;
+        }
+    };
+    prefetch(e);
+    for (; e < c.N; e += stride) {
+        EnvInputs cur = nxt;
+        prefetch(e + stride);
+        __syncwarp();
+        if (lane < nvec) reinterpret_cast<uint4*>(sm.sg)[lane] = cur.gv;
+        __syncwarp();
+        env_step<32, NB>(grp, c, sm, cur.rec, cur.act, cur.k0, cur.k1, rewards + e * n, dones + e * n, st);
+        if (lane < nvec) reinterpret_cast<uint4*>(ground + e * c.GS)[lane] = reinterpret_cast<const uint4*>(sm.sg)[lane];
+        if (lane < n) drones[e * n + lane] = cur.rec;
+        if (obs != nullptr) {
+            int mark;
+            obs_publish(c, sm, lane, cur.rec, mark);
+            __syncwarp();
+            obs_tiles(c, sm, obs, e, tile, 0, 1, lane);
+            __syncwarp();
+            if (mark >= 0) sm.code[mark] = 0;
+        }
+        ++env_steps;
+    }
+    tile_drain(lane);
+    flush_stats(st, env_steps, stats, lane);
+}
+
+template <int NB>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+k_reset_warp(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint32_t* __restrict__ drones,
+             const uint32_t* __restrict__ keys, unsigned long long* __restrict__ stats) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    unsigned char* base = smem_raw + (size_t)warp * c.group_bytes;
+    const Smem sm = carve(base, c);
+    Group<32> grp{nullptr};
+    const int nvec = c.GS >> 4, n = c.n;
+    const long long stride = (long long)gridDim.x * kWarpsPerBlock;
+    unsigned resets = 0;
+    for (long long e = (long long)blockIdx.x * kWarpsPerBlock + warp; e < c.N; e += stride) {
+        const uint2 kk = *reinterpret_cast<const uint2*>(keys + 2 * e);
+        __syncwarp();
+        if (lane < nvec) reinterpret_cast<uint4*>(sm.sg)[lane] = make_uint4(0, 0, 0, 0);
+        __syncwarp();
+        uint32_t rec = 0;
+        env_reset<32, NB>(grp, c, sm, rec, kk.x, kk.y);
+        if (lane < nvec) reinterpret_cast<uint4*>(ground + e * c.GS)[lane] = reinterpret_cast<const uint4*>(sm.sg)[lane];
+        if (lane < n) drones[e * n + lane] = rec;
+        ++resets;
+    }
+    if (lane == 0 && resets) atomicAdd(stats + DRL_STAT_RESETS, (unsigned long long)resets);
+}
+
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+k_obs_warp(const __grid_constant__ DevCfg c, const uint8_t* __restrict__ ground, const uint32_t* __restrict__ drones,
+           float* __restrict__ obs) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    unsigned char* base = smem_raw + (size_t)warp * c.group_bytes;
+    const Smem sm = carve(base, c);
+    float* tile = reinterpret_cast<float*>(base + c.off_tile);
+    zero_code(c, sm, lane, 32);
+    const int nvec = c.GS >> 4, n = c.n;
+    const long long stride = (long long)gridDim.x * kWarpsPerBlock;
+    for (long long e = (long long)blockIdx.x * kWarpsPerBlock + warp; e < c.N; e += stride) {
+        __syncwarp();
+        if (lane < nvec) reinterpret_cast<uint4*>(sm.sg)[lane] = reinterpret_cast<const uint4*>(ground + e * c.GS)[lane];
+        const uint32_t rec = lane < n ? drones[e * n + lane] : 0u;
+        int mark;
+        obs_publish(c, sm, lane, rec, mark);
+        __syncwarp();
+        obs_tiles(c, sm, obs, e, tile, 0, 1, lane);
+        __syncwarp();
+        if (mark >= 0) sm.code[mark] = 0;
+    }
+    tile_drain(lane);
+}
+
+// ---- CTA-per-env kernels (larger grids) -------------------------------------------------------
+
+template <int NB>
+__global__ void __launch_bounds__(kCtaThreads)
+k_step_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint32_t* __restrict__ drones,
+           const uint32_t* __restrict__ keys, const int8_t* __restrict__ actions, float* __restrict__ rewards,
+           uint8_t* __restrict__ dones, float* __restrict__ obs, unsigned long long* __restrict__ stats) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr int T = kCtaThreads;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const Smem sm = carve(smem_raw, c);
+    float* tile = reinterpret_cast<float*>(smem_raw + c.off_tile + (size_t)warp * c.tile_stride);
+    Group<T> grp{reinterpret_cast<unsigned long long*>(smem_raw + c.off_red)};
+    zero_code(c, sm, threadIdx.x, T);
+    const int nvec = c.GS >> 4, n = c.n;
+    Stats st;
+    unsigned env_steps = 0;
+    for (long long e = blockIdx.x; e < c.N; e += gridDim.x) {
+        for (int i = threadIdx.x; i < nvec; i += T)
+            reinterpret_cast<uint4*>(sm.sg)[i] = reinterpret_cast<const uint4*>(ground + e * c.GS)[i];
+        uint32_t rec = 0;
+        int act = 4;
+        if (threadIdx.x < n) {
+            rec = drones[e * n + threadIdx.x];
+            act = actions[e * n + threadIdx.x];
+        }
+        const uint2 kk = *reinterpret_cast<const uint2*>(keys + 2 * e);
+        __syncthreads();
+        env_step<T, NB>(grp, c, sm, rec, act, kk.x, kk.y, rewards + e * n, dones + e * n, st);
+        for (int i = threadIdx.x; i < nvec; i += T)
+            reinterpret_cast<uint4*>(ground + e * c.GS)[i] = reinterpret_cast<const uint4*>(sm.sg)[i];
+        if (threadIdx.x < n) drones[e * n + threadIdx.x] = rec;
+        if (obs != nullptr) {
+            int mark = -1;
+            if (warp == 0) obs_publish(c, sm, lane, rec, mark);
+            __syncthreads();
+            obs_tiles(c, sm, obs, e, tile, warp, T / 32, lane);
+            __syncthreads();
+            if (mark >= 0) sm.code[mark] = 0;
+        }
+        if (threadIdx.x == 0) ++env_steps;
+    }
+    tile_drain(lane);
+    if (warp == 0) flush_stats(st, env_steps, stats, lane);
+}
+
+template <int NB>
+__global__ void __launch_bounds__(kCtaThreads)
+k_reset_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint32_t* __restrict__ drones,
+            const uint32_t* __restrict__ keys, unsigned long long* __restrict__ stats) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr int T = kCtaThreads;
+    const Smem sm = carve(smem_raw, c);
+    Group<T> grp{reinterpret_cast<unsigned long long*>(smem_raw + c.off_red)};
+    const int nvec = c.GS >> 4, n = c.n;
+    unsigned resets = 0;
+    for (long long e = blockIdx.x; e < c.N; e += gridDim.x) {
+        const uint2 kk = *reinterpret_cast<const uint2*>(keys + 2 * e);
+        for (int i = threadIdx.x; i < nvec; i += T) reinterpret_cast<uint4*>(sm.sg)[i] = make_uint4(0, 0, 0, 0);
+        __syncthreads();
+        uint32_t rec = 0;
+        env_reset<T, NB>(grp, c, sm, rec, kk.x, kk.y);
+        for (int i = threadIdx.x; i < nvec; i += T)
+            reinterpret_cast<uint4*>(ground + e * c.GS)[i] = reinterpret_cast<const uint4*>(sm.sg)[i];
+        if (threadIdx.x < n) drones[e * n + threadIdx.x] = rec;
+        ++resets;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0 && resets) atomicAdd(stats + DRL_STAT_RESETS, (unsigned long long)resets);
+}
+
+__global__ void __launch_bounds__(kCtaThreads)
+k_obs_cta(const __grid_constant__ DevCfg c, const uint8_t* __restrict__ ground, const uint32_t* __restrict__ drones,
+          float* __restrict__ obs) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr int T = kCtaThreads;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const Smem sm = carve(smem_raw, c);
+    float* tile = reinterpret_cast<float*>(smem_raw + c.off_tile + (size_t)warp * c.tile_stride);
+    zero_code(c, sm, threadIdx.x, T);
+    const int nvec = c.GS >> 4, n = c.n;
+    for (long long e = blockIdx.x; e < c.N; e += gridDim.x) {
+        __syncthreads();
+        for (int i = threadIdx.x; i < nvec; i += T)
+            reinterpret_cast<uint4*>(sm.sg)[i] = reinterpret_cast<const uint4*>(ground + e * c.GS)[i];
+        int mark = -1;
+        if (warp == 0) {
+            const uint32_t rec = lane < n ? drones[e * n + lane] : 0u;
+            obs_publish(c, sm, lane, rec, mark);
+        }
+        __syncthreads();
+        obs_tiles(c, sm, obs, e, tile, warp, T / 32, lane);
+        __syncthreads();
+        if (mark >= 0) sm.code[mark] = 0;
+    }
+    tile_drain(lane);
+}
+
+// ---- key / action derivation --------------------------------------------------------------------
+
+// keys_out[e] = split(key, Ng)[off + e]: flat words 2(off+e), 2(off+e)+1 of random_bits(key, 2 Ng)
+__global__ void k_split_keys(uint32_t k0, uint32_t k1, long long Ng, long long off, long long Nl,
+                             uint32_t* __restrict__ out) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;   // local flat word
+    if (i >= 2 * Nl) return;
+    out[i] = drl_random_bits_at(k0, k1, (uint64_t)(2 * Ng), (uint64_t)(2 * off + i));
+}
+
+// actions_out = int8(randint(key, (Ng, n), 0, maxval))[off : off + Nl]; (a0,a1),(b0,b1) = split(key)
+__global__ void k_randint(uint32_t a0, uint32_t a1, uint32_t b0, uint32_t b1, long long total, long long first,
+                          long long count, uint32_t span, uint32_t mult, int8_t* __restrict__ out) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    const uint32_t hi = drl_random_bits_at(a0, a1, (uint64_t)total, (uint64_t)(first + i));
+    const uint32_t lo = drl_random_bits_at(b0, b1, (uint64_t)total, (uint64_t)(first + i));
+    const uint32_t v = ((hi % span) * mult + (lo % span)) % span;
+    out[i] = (int8_t)v;
+}
+
+// =================================================================================================
+// host side / C ABI
+// =================================================================================================
+
+struct drl_env {
+    drl_config cfg;
+    DevCfg dc;
+    bool warp_mode;
+    int nb;               // threefry blocks per thread (template instance)
+    int smem_bytes;       // dynamic shared memory per CTA
+    int grid_step, grid_reset, grid_obs;
+    int sm_count;
+    uint8_t* d_ground;
+    uint32_t* d_drones;
+    unsigned long long* d_stats;
+    // scratch owned by the handle for the *_host entry points
+    uint32_t* s_keys;
+    int8_t* s_actions;
+    float* s_rewards;
+    uint8_t* s_dones;
+    char err[512];
+};
+
+static char g_create_err[512] = "";
+
+static int fail(drl_env* env, int code, const char* fmt, const char* a = "", long long b = 0, long long c = 0) {
+    char* dst = env ? env->err : g_create_err;
+    snprintf(dst, 512, fmt, a, b, c);
+    return code;
+}
+
+#define CUDA_TRY(env, call)                                                                  \
+    do {                                                                                     \
+        cudaError_t e_ = (call);                                                             \
+        if (e_ != cudaSuccess) return fail((env), DRL_ECUDA, "%s failed: CUDA error %lld", #call, (long long)e_); \
+    } while (0)
+
+static uint32_t magic(int d) { return d <= 1 ? 0u : (uint32_t)((1ull << 32) / (unsigned)d + 1ull); }
+static int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+typedef void (*step_fn)(DevCfg, uint8_t*, uint32_t*, const uint32_t*, const int8_t*, float*, uint8_t*, float*,
+                        unsigned long long*);
+typedef void (*reset_fn)(DevCfg, uint8_t*, uint32_t*, const uint32_t*, unsigned long long*);
+typedef void (*obs_fn)(DevCfg, const uint8_t*, const uint32_t*, float*);
+
+static step_fn pick_step(const drl_env* e) {
+    if (e->warp_mode) return e->nb == 1 ? (step_fn)k_step_warp<1> : (step_fn)k_step_warp<2>;
+    return e->nb == 2 ? (step_fn)k_step_cta<2> : e->nb == 8 ? (step_fn)k_step_cta<8> : (step_fn)k_step_cta<16>;
+}
+static reset_fn pick_reset(const drl_env* e) {
+    if (e->warp_mode) return e->nb == 1 ? (reset_fn)k_reset_warp<1> : (reset_fn)k_reset_warp<2>;
+    return e->nb == 2 ? (reset_fn)k_reset_cta<2> : e->nb == 8 ? (reset_fn)k_reset_cta<8> : (reset_fn)k_reset_cta<16>;
+}
+static obs_fn pick_obs(const drl_env* e) { return e->warp_mode ? (obs_fn)k_obs_warp : (obs_fn)k_obs_cta; }
+
+extern "C" {
+
+int drl_abi_version(void) { return DRL_ABI_VERSION; }
+const char* drl_version(void) { return "dronerl_b200 0.1 (sm_100a)"; }
+const char* drl_last_error(const drl_env* env) { return env ? env->err : g_create_err; }
+
+void drl_prng_key(uint64_t seed, uint32_t out[2]) {
+    out[0] = (uint32_t)(seed >> 32);
+    out[1] = (uint32_t)(seed & 0xFFFFFFFFull);
+}
+
+void drl_split2(const uint32_t key[2], uint32_t new_key[2], uint32_t sub_key[2]) {
+    drl_split2_hd(key[0], key[1], new_key[0], new_key[1], sub_key[0], sub_key[1]);
+}
+
+int drl_create(const drl_config* cfg, drl_env** out) {
+    if (!cfg || !out) return fail(nullptr, DRL_EINVAL, "drl_create: null argument%s");
+    *out = nullptr;
+    const int G = cfg->grid_size, n = cfg->n_drones, r = cfg->window_radius;
+    if (G < 1 || n < 1 || r < 0) return fail(nullptr, DRL_EINVAL, "grid_size, n_drones must be >= 1 and window_radius >= 0%s");
+    if (cfg->packets_factor < 0 || cfg->dropzones_factor < 0 || cfg->stations_factor < 0 || cfg->skyscrapers_factor < 0)
+        return fail(nullptr, DRL_EINVAL, "object factors must be >= 0%s");
+    const long long G2 = (long long)G * G;
+    // reference reset validation, jax_impl/env/env.py:91-104
+    const long long n_obj = (long long)(cfg->packets_factor + cfg->dropzones_factor + cfg->stations_factor +
+                                        cfg->skyscrapers_factor) * n;
+    if (n_obj > G2)
+        return fail(nullptr, DRL_EPARAMS, "Grid supports only %s%lld positions but %lld objects were attempted to be placed.",
+                    "", G2, n_obj);
+    if (n > G2)
+        return fail(nullptr, DRL_EPARAMS, "Grid supports only %s%lld positions but %lld drones were attempted to be placed.",
+                    "", G2, (long long)n);
+    if (cfg->packets_factor < 1)
+        return fail(nullptr, DRL_EINVAL, "packets_factor must be >= 1 (the reference's step cannot build its fill vector otherwise)%s");
+    if (n > 32) return fail(nullptr, DRL_EINVAL, "n_drones > 32 is not supported by this build%s");
+    if (G > 90) return fail(nullptr, DRL_EINVAL, "grid_size > 90 is not supported by this build%s");
+    if (2 * r + 1 > 63) return fail(nullptr, DRL_EINVAL, "window_radius > 31 is not supported by this build%s");
+    if (cfg->num_envs < 1 || cfg->env_offset < 0 || cfg->num_envs_global < cfg->env_offset + cfg->num_envs)
+        return fail(nullptr, DRL_EINVAL, "bad env slice: need 1 <= num_envs and env_offset + num_envs <= num_envs_global%s");
+    if (cfg->num_envs_global > (1ll << 30))
+        return fail(nullptr, DRL_EINVAL, "num_envs_global > 2^30 would overflow the 32-bit threefry counters of split()%s");
+
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0 || cfg->device < 0 || cfg->device >= ndev) {
+        cudaGetLastError();
+        return fail(nullptr, DRL_ENODEVICE, "no usable CUDA device (count %s%lld, requested %lld); there is no CPU fallback", "",
+                    (long long)ndev, (long long)cfg->device);
+    }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, cfg->device) != cudaSuccess || prop.major != 10)
+        return fail(nullptr, DRL_ENODEVICE, "device %s%lld is not an sm_100 (Blackwell) GPU; this library ships sm_100a code only", "",
+                    (long long)cfg->device);
+    CUDA_TRY(nullptr, cudaSetDevice(cfg->device));
+
+    drl_env* e = new (std::nothrow) drl_env();
+    if (!e) return fail(nullptr, DRL_EINVAL, "out of host memory%s");
+    memset(e, 0, sizeof(*e));
+    e->cfg = *cfg;
+    e->sm_count = prop.multiProcessorCount;
+    DevCfg& c = e->dc;
+    c.G = G; c.G2 = (int)G2; c.H = (int)((G2 + 1) / 2); c.GS = round_up((int)G2, 16);
+    c.n = n; c.r = r; c.W = 2 * r + 1; c.W2 = c.W * c.W; c.center = r * c.W + r;
+    c.k_spawn = cfg->packets_factor * n;
+    c.k_reset[0] = cfg->packets_factor * n; c.k_reset[1] = cfg->dropzones_factor * n;
+    c.k_reset[2] = cfg->stations_factor * n; c.k_reset[3] = cfg->skyscrapers_factor * n;
+    c.charge = cfg->charge; c.discharge = cfg->discharge;
+    c.rw_pickup = cfg->pickup_reward; c.rw_delivery = cfg->delivery_reward;
+    c.rw_crash = cfg->crash_reward; c.rw_charge = cfg->charge_reward;
+    c.mulG = magic(G); c.mulW = magic(c.W); c.mulW2 = magic(c.W2);
+    c.N = cfg->num_envs;
+
+    e->warp_mode = G2 <= 128;
+    const int cell_bytes = c.W2 * 24;
+    if (e->warp_mode) {
+        e->nb = c.H <= 32 ? 1 : 2;
+        int td = n;
+        if (td * cell_bytes > 12288) { td = 8192 / cell_bytes; if (td > 1) td &= ~1; if (td < 1) td = 1; }
+        c.tile_drones = td;
+    } else {
+        e->nb = c.H <= 2 * kCtaThreads ? 2 : c.H <= 8 * kCtaThreads ? 8 : 16;
+        c.tile_drones = (n >= 2 && 2 * cell_bytes <= 12288) ? 2 : 1;
+    }
+    c.tile_stride = round_up(c.tile_drones * cell_bytes, 128);
+    c.off_code = c.GS;
+    c.off_sdr = c.off_code + round_up((int)G2, 16);
+    c.off_sdf = c.off_sdr + 128;
+    c.off_misc = c.off_sdf + 128;
+    c.off_red = c.off_misc + 16;
+    c.off_tile = round_up(c.off_red + 2 * (kCtaThreads / 32) * 8, 128);
+    if (e->warp_mode) {
+        c.group_bytes = c.off_tile + c.tile_stride;
+        e->smem_bytes = c.group_bytes * kWarpsPerBlock;
+    } else {
+        c.group_bytes = c.off_tile + c.tile_stride * (kCtaThreads / 32);
+        e->smem_bytes = c.group_bytes;
+    }
+    if (e->smem_bytes > (int)prop.sharedMemPerBlockOptin) {
+        const long long need = e->smem_bytes;
+        delete e;
+        return fail(nullptr, DRL_EINVAL, "configuration needs %s%lld bytes of shared memory per CTA (limit %lld)", "",
+                    need, (long long)prop.sharedMemPerBlockOptin);
+    }
+
+    const int threads = e->warp_mode ? kWarpsPerBlock * 32 : kCtaThreads;
+    const void* fns[3] = {(const void*)pick_step(e), (const void*)pick_reset(e), (const void*)pick_obs(e)};
+    int* grids[3] = {&e->grid_step, &e->grid_reset, &e->grid_obs};
+    const long long units = e->warp_mode ? (c.N + kWarpsPerBlock - 1) / kWarpsPerBlock : c.N;
+    for (int i = 0; i < 3; ++i) {
+        cudaError_t ce = cudaFuncSetAttribute(fns[i], cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem_bytes);
+        int per_sm = 0;
+        if (ce == cudaSuccess) ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fns[i], threads, e->smem_bytes);
+        if (ce != cudaSuccess || per_sm < 1) {
+            delete e;
+            return fail(nullptr, DRL_ECUDA, "kernel %s setup failed (CUDA error %lld, blocks/SM %lld)", i == 0 ? "step" : i == 1 ? "reset" : "obs",
+                        (long long)ce, (long long)per_sm);
+        }
+        const long long resident = (long long)per_sm * e->sm_count;
+        *grids[i] = (int)(units < resident ? units : resident);
+    }
+    if (cudaMalloc(&e->d_stats, DRL_NUM_STATS * sizeof(unsigned long long)) != cudaSuccess ||
+        cudaMemset(e->d_stats, 0, DRL_NUM_STATS * sizeof(unsigned long long)) != cudaSuccess) {
+        delete e;
+        return fail(nullptr, DRL_ECUDA, "cudaMalloc of the statistics block failed%s");
+    }
+    *out = e;
+    return DRL_OK;
+}
+
+void drl_destroy(drl_env* env) {
+    if (!env) return;
+    cudaSetDevice(env->cfg.device);
+    cudaFree(env->d_stats);
+    cudaFree(env->s_keys);
+    cudaFree(env->s_actions);
+    cudaFree(env->s_rewards);
+    cudaFree(env->s_dones);
+    delete env;
+}
+
+int drl_get_layout(const drl_env* env, drl_layout* out) {
+    if (!env || !out) return DRL_EINVAL;
+    const DevCfg& c = env->dc;
+    out->ground_stride = c.GS;
+    out->ground_bytes = c.N * c.GS;
+    out->drones_bytes = c.N * c.n * 4;
+    out->keys_bytes = c.N * 8;
+    out->actions_bytes = c.N * c.n;
+    out->rewards_bytes = c.N * c.n * 4;
+    out->dones_bytes = c.N * c.n;
+    out->obs_bytes = c.N * c.n * (long long)c.W2 * 24;
+    out->algorithmic_bytes_per_env_step = 24ll * c.n * c.W2 + 2ll * c.G2 + 14ll * c.n;
+    return DRL_OK;
+}
+
+int drl_bind_state(drl_env* env, void* d_ground, void* d_drones) {
+    if (!env) return DRL_EINVAL;
+    if (!d_ground || !d_drones) return fail(env, DRL_EINVAL, "drl_bind_state: null state pointer%s");
+    if (((uintptr_t)d_ground & 15) || ((uintptr_t)d_drones & 3))
+        return fail(env, DRL_EINVAL, "drl_bind_state: ground must be 16-byte and drones 4-byte aligned%s");
+    env->d_ground = (uint8_t*)d_ground;
+    env->d_drones = (uint32_t*)d_drones;
+    return DRL_OK;
+}
+
+static int check_launch(drl_env* env, const char* what) {
+    cudaError_t ce = cudaGetLastError();
+    if (ce != cudaSuccess) return fail(env, DRL_ECUDA, "launch of %s failed: CUDA error %lld", what, (long long)ce);
+    return DRL_OK;
+}
+
+int drl_split_n(const uint32_t key[2], int64_t num, int64_t offset, int64_t count, void* d_out, void* stream) {
+    if (!key || !d_out || num < 1 || offset < 0 || count < 0 || offset + count > num || num > (1ll << 30)) return DRL_EINVAL;
+    if (count == 0) return DRL_OK;
+    k_split_keys<<<(unsigned)((2 * count + 255) / 256), 256, 0, (cudaStream_t)stream>>>(key[0], key[1], num, offset, count,
+                                                                                       (uint32_t*)d_out);
+    return cudaGetLastError() == cudaSuccess ? DRL_OK : DRL_ECUDA;
+}
+
+int drl_randint_n(const uint32_t key[2], int64_t total, int64_t first, int64_t count, int32_t maxval, void* d_out,
+                  void* stream) {
+    if (!key || !d_out || total < 1 || first < 0 || count < 0 || first + count > total || total >= (1ll << 32) ||
+        maxval < 1 || maxval > 127)
+        return DRL_EINVAL;
+    if (count == 0) return DRL_OK;
+    uint32_t k1[2], k2[2];
+    drl_split2(key, k1, k2);   // _randint: k1, k2 = split(key)
+    const uint32_t span = (uint32_t)maxval;
+    uint32_t mult = 65536u % span;
+    mult = (mult * mult) % span;
+    k_randint<<<(unsigned)((count + 255) / 256), 256, 0, (cudaStream_t)stream>>>(k1[0], k1[1], k2[0], k2[1], total, first,
+                                                                                count, span, mult, (int8_t*)d_out);
+    return cudaGetLastError() == cudaSuccess ? DRL_OK : DRL_ECUDA;
+}
+
+int drl_split_keys(drl_env* env, const uint32_t key[2], void* d_keys_out, void* stream) {
+    if (!env || !key || !d_keys_out) return DRL_EINVAL;
+    CUDA_TRY(env, cudaSetDevice(env->cfg.device));
+    const int rc = drl_split_n(key, env->cfg.num_envs_global, env->cfg.env_offset, env->dc.N, d_keys_out, stream);
+    return rc ? fail(env, rc, "drl_split_keys: derivation kernel failed%s") : DRL_OK;
+}
+
+int drl_randint_actions(drl_env* env, const uint32_t key[2], int32_t maxval, void* d_actions_out, void* stream) {
+    if (!env || !key || !d_actions_out) return DRL_EINVAL;
+    CUDA_TRY(env, cudaSetDevice(env->cfg.device));
+    const long long n = env->dc.n;
+    const int rc = drl_randint_n(key, env->cfg.num_envs_global * n, env->cfg.env_offset * n, env->dc.N * n, maxval,
+                                 d_actions_out, stream);
+    return rc ? fail(env, rc, "drl_randint_actions: bad maxval (1..127), too many actions (>= 2^32) or launch failure%s") : DRL_OK;
+}
+
+int drl_reset(drl_env* env, const void* d_keys, void* stream) {
+    if (!env || !d_keys) return DRL_EINVAL;
+    if (!env->d_ground) return fail(env, DRL_ESTATE, "drl_reset: state not bound (call drl_bind_state)%s");
+    CUDA_TRY(env, cudaSetDevice(env->cfg.device));
+    const int threads = env->warp_mode ? kWarpsPerBlock * 32 : kCtaThreads;
+    pick_reset(env)<<<env->grid_reset, threads, env->smem_bytes, (cudaStream_t)stream>>>(
+        env->dc, env->d_ground, env->d_drones, (const uint32_t*)d_keys, env->d_stats);
+    return check_launch(env, "reset kernel");
+}
+
+int drl_step(drl_env* env, const void* d_keys, const void* d_actions, void* d_rewards, void* d_dones, void* d_obs,
+             void* stream) {
+    if (!env || !d_keys || !d_actions || !d_rewards || !d_dones) return DRL_EINVAL;
+    if (!env->d_ground) return fail(env, DRL_ESTATE, "drl_step: state not bound (call drl_bind_state)%s");
+    if ((uintptr_t)d_obs & 7) return fail(env, DRL_EINVAL, "drl_step: obs must be 8-byte aligned%s");
+    CUDA_TRY(env, cudaSetDevice(env->cfg.device));
+    const int threads = env->warp_mode ? kWarpsPerBlock * 32 : kCtaThreads;
+    pick_step(env)<<<env->grid_step, threads, env->smem_bytes, (cudaStream_t)stream>>>(
+        env->dc, env->d_ground, env->d_drones, (const uint32_t*)d_keys, (const int8_t*)d_actions, (float*)d_rewards,
+        (uint8_t*)d_dones, (float*)d_obs, env->d_stats);
+    return check_launch(env, "step kernel");
+}
+
+int drl_get_obs(drl_env* env, void* d_obs, void* stream) {
+    if (!env || !d_obs) return DRL_EINVAL;
+    if (!env->d_ground) return fail(env, DRL_ESTATE, "drl_get_obs: state not bound (call drl_bind_state)%s");
+    if ((uintptr_t)d_obs & 7) return fail(env, DRL_EINVAL, "drl_get_obs: obs must be 8-byte aligned%s");
+    CUDA_TRY(env, cudaSetDevice(env->cfg.device));
+    const int threads = env->warp_mode ? kWarpsPerBlock * 32 : kCtaThreads;
+    pick_obs(env)<<<env->grid_obs, threads, env->smem_bytes, (cudaStream_t)stream>>>(env->dc, env->d_ground, env->d_drones,
+                                                                                  (float*)d_obs);
+    return check_launch(env, "obs kernel");
+}
+
+static int ensure_scratch(drl_env* env) {
+    if (env->s_keys) return DRL_OK;
+    const DevCfg& c = env->dc;
+    CUDA_TRY(env, cudaMalloc(&env->s_keys, c.N * 8));
+    CUDA_TRY(env, cudaMalloc(&env->s_actions, c.N * c.n));
+    CUDA_TRY(env, cudaMalloc(&env->s_rewards, c.N * c.n * 4));
+    CUDA_TRY(env, cudaMalloc(&env->s_dones, c.N * c.n));
+    return DRL_OK;
+}
+
+int drl_step_host(drl_env* env, const uint32_t key[2], const int8_t* h_actions, float* h_rewards, uint8_t* h_dones,
+                  void* d_obs, float* h_obs, void* stream) {
+    if (!env || !key || !h_actions || !h_rewards || !h_dones) return DRL_EINVAL;
+    if (h_obs && !d_obs) return fail(env, DRL_EINVAL, "drl_step_host: h_obs needs a device obs buffer too%s");
+    CUDA_TRY(env, cudaSetDevice(env->cfg.device));
+    int rc = ensure_scratch(env);
+    if (rc) return rc;
+    const DevCfg& c = env->dc;
+    cudaStream_t s = (cudaStream_t)stream;
+    CUDA_TRY(env, cudaMemcpyAsync(env->s_actions, h_actions, c.N * c.n, cudaMemcpyHostToDevice, s));
+    rc = drl_split_keys(env, key, env->s_keys, stream);
+    if (rc) return rc;
+    rc = drl_step(env, env->s_keys, env->s_actions, env->s_rewards, env->s_dones, d_obs, stream);
+    if (rc) return rc;
+    CUDA_TRY(env, cudaMemcpyAsync(h_rewards, env->s_rewards, c.N * c.n * 4, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(env, cudaMemcpyAsync(h_dones, env->s_dones, c.N * c.n, cudaMemcpyDeviceToHost, s));
+    if (h_obs) CUDA_TRY(env, cudaMemcpyAsync(h_obs, d_obs, c.N * c.n * (long long)c.W2 * 24, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(env, cudaStreamSynchronize(s));
+    return DRL_OK;
+}
+
+int drl_rollout_random(drl_env* env, uint32_t rng[2], int32_t steps, int32_t reset_every, int64_t step0, void* d_keys,
+                       void* d_actions, void* d_rewards, void* d_dones, void* d_obs, void* stream) {
+    if (!env || !rng || steps < 0 || !d_keys || !d_actions) return DRL_EINVAL;
+    int launches = 0;
+    for (int32_t t = 0; t < steps; ++t) {
+        uint32_t nk[2], sub[2];
+        drl_split2(rng, nk, sub);                                  // rng, key = split(rng)   train_jax.py:43
+        rng[0] = nk[0]; rng[1] = nk[1];
+        int rc = drl_randint_actions(env, sub, 5, d_actions, stream);   // randint(key, (N, n), 0, 5)  :44
+        if (rc) return rc;
+        drl_split2(rng, nk, sub);                                  // rng, key = split(rng)   :52
+        rng[0] = nk[0]; rng[1] = nk[1];
+        rc = drl_split_keys(env, sub, d_keys, stream);             // split(key, N)           :53
+        if (rc) return rc;
+        rc = drl_step(env, d_keys, d_actions, d_rewards, d_dones, d_obs, stream);   // :54-55
+        if (rc) return rc;
+        launches += 3;
+        drl_split2(rng, nk, sub);                                  // rng, key = split(rng)   :82 (the trainer's batch key)
+        rng[0] = nk[0]; rng[1] = nk[1];
+        if (reset_every > 0 && (step0 + t) % reset_every == 0) {   // :101-113 (resets with the carried rng itself)
+            rc = drl_split_keys(env, rng, d_keys, stream);
+            if (rc) return rc;
+            rc = drl_reset(env, d_keys, stream);
+            if (rc) return rc;
+            launches += 2;
+            if (d_obs) {
+                rc = drl_get_obs(env, d_obs, stream);
+                if (rc) return rc;
+                launches += 1;
+            }
+        }
+    }
+    return launches;
+}
+
+int drl_stats_read(drl_env* env, uint64_t* h_out, void* stream) {
+    if (!env || !h_out) return DRL_EINVAL;
+    CUDA_TRY(env, cudaSetDevice(env->cfg.device));
+    CUDA_TRY(env, cudaMemcpyAsync(h_out, env->d_stats, DRL_NUM_STATS * sizeof(uint64_t), cudaMemcpyDeviceToHost,
+                                  (cudaStream_t)stream));
+    CUDA_TRY(env, cudaStreamSynchronize((cudaStream_t)stream));
+    return DRL_OK;
+}
+
+int drl_stats_clear(drl_env* env, void* stream) {
+    if (!env) return DRL_EINVAL;
+    CUDA_TRY(env, cudaSetDevice(env->cfg.device));
+    CUDA_TRY(env, cudaMemsetAsync(env->d_stats, 0, DRL_NUM_STATS * sizeof(uint64_t), (cudaStream_t)stream));
+    return DRL_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,498 @@
+// Device code of the batched DroneRL env for sm_100a: reset / step / get_obs.
+//
+// Semantics follow /root/reference/jax_impl/env/env.py (spawn :40-61, spawn_air
+// :63-86, reset :89-135, step :137-250, get_obs :274-309) bit-for-bit, but the
+// formulation is native to the GPU:
+//   * one cooperating thread group per env -- a warp (T = 32) for grids up to
+//     128 cells, a 256-thread CTA for larger ones; the env's ground lives in
+//     shared memory for the whole step, drones live in the lanes of one warp;
+//   * drone/drone collisions and the "last scatter update wins" rule of the
+//     reference's masks are warp match_any groups (no sort, no unique);
+//   * top_k over ``log(free)+uniform`` is an integer arg-max over
+//     (23-bit mantissa + 1 | reversed cell index) keys -- exactly the order of
+//     jax.lax.top_k incl. ties and the -inf tail -- extracted rank by rank only
+//     as far as a non-zero fill (or an erasing zero) needs it;
+//   * threefry noise is generated lazily (only when something spawns) with the
+//     cell ownership chosen so that every lane consumes both words of the
+//     blocks it hashes;
+//   * observations are composed per tile of drones in shared memory and shipped
+//     with one TMA bulk store (cp.async.bulk.global.shared::cta) per tile.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "threefry.cuh"
+
+namespace drl {
+
+constexpr unsigned FULL = 0xFFFFFFFFu;
+enum : int { SKY = 2, STATION = 3, DROPZONE = 4, PACKET = 5 };
+enum : int { A_LEFT = 0, A_DOWN = 1, A_RIGHT = 2, A_UP = 3 };
+constexpr int kCtaThreads = 256;
+constexpr int kWarpsPerBlock = 8;
+
+struct DevCfg {
+    int G, G2, H, GS;          // grid side, cells, ceil(cells/2) (threefry blocks per noise vector), ground row stride
+    int n, r, W, W2, center;   // drones, window radius, 2r+1, W*W, r*W+r
+    int k_spawn;               // packets_factor*n: length of both fill vectors in step (env.py:198,206)
+    int k_reset[4];            // packets, dropzones, stations, skyscrapers counts in reset order
+    int charge, discharge;
+    float rw_pickup, rw_delivery, rw_crash, rw_charge;
+    uint32_t mulG, mulW, mulW2;  // magic multipliers: x / d == umulhi(x, mul) for x*d < 2^32
+    int tile_drones;           // drones per obs tile
+    int tile_stride;           // bytes reserved per obs tile buffer
+    // shared-memory carve-up (bytes from the group's base)
+    int off_code, off_sdr, off_sdf, off_misc, off_red, off_tile;
+    int group_bytes;           // warp mode: bytes per warp; CTA mode: bytes per CTA
+    long long N;               // local envs
+};
+
+struct Stats {
+    unsigned dones = 0, crashes = 0, pickups = 0, deliveries = 0, charging = 0, respawn_pickups = 0;
+};
+
+__device__ __forceinline__ uint32_t fdiv(uint32_t x, int d, uint32_t mul) { return d == 1 ? x : __umulhi(x, mul); }
+
+// ---- group primitives: warp (T == 32) or CTA of T threads ----------------------------------
+
+template <int T>
+struct Group {
+    static constexpr bool kWarp = (T == 32);
+    static constexpr int kWarps = T / 32;
+    unsigned long long* red;   // [2][kWarps] scratch (CTA mode)
+    int par = 0;
+
+    __device__ __forceinline__ static int tid() { return kWarp ? (int)(threadIdx.x & 31) : (int)threadIdx.x; }
+    __device__ __forceinline__ static void sync() {
+        if (kWarp) __syncwarp(); else __syncthreads();
+    }
+    // lexicographic max of (hi, lo) pairs over the group; every thread gets the result
+    __device__ __forceinline__ void max_pair(uint32_t hi, uint32_t lo, uint32_t& mh, uint32_t& ml) {
+        mh = __reduce_max_sync(FULL, hi);
+        ml = __reduce_max_sync(FULL, hi == mh ? lo : 0u);
+        if (!kWarp) {
+            const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+            unsigned long long* b = red + par * kWarps;
+            if (lane == 0) b[warp] = ((unsigned long long)mh << 32) | ml;
+            __syncthreads();
+            unsigned long long m = 0;
+#pragma unroll
+            for (int w = 0; w < kWarps; ++w) { unsigned long long v = b[w]; m = v > m ? v : m; }
+            par ^= 1;
+            mh = (uint32_t)(m >> 32);
+            ml = (uint32_t)m;
+        }
+    }
+    __device__ __forceinline__ int sum(int v) {
+        int s = __reduce_add_sync(FULL, v);
+        if (!kWarp) {
+            const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+            unsigned long long* b = red + par * kWarps;
+            if (lane == 0) b[warp] = (unsigned long long)(unsigned)s;
+            __syncthreads();
+            s = 0;
+#pragma unroll
+            for (int w = 0; w < kWarps; ++w) s += (int)b[w];
+            par ^= 1;
+        }
+        return s;
+    }
+};
+
+struct Smem {
+    uint8_t* sg;      // ground, GS bytes (16-B aligned)
+    uint8_t* code;    // per-cell scratch: survivor marks during respawn, drone index + 1 for obs; zero between uses
+    uint32_t* sdr;    // final drone records, [32]
+    float* sdf;       // charge / 100 per drone, [32]
+    uint32_t* misc;   // CTA-mode broadcast words
+};
+
+__device__ __forceinline__ Smem carve(unsigned char* base, const DevCfg& c) {
+    Smem s;
+    s.sg = base;
+    s.code = base + c.off_code;
+    s.sdr = reinterpret_cast<uint32_t*>(base + c.off_sdr);
+    s.sdf = reinterpret_cast<float*>(base + c.off_sdf);
+    s.misc = reinterpret_cast<uint32_t*>(base + c.off_misc);
+    return s;
+}
+
+// Cell owned by slot s of thread tid: threefry block b = tid + T*(s/2) yields the noise of
+// cells b (word 0) and b + H (word 1) -- jax's original random_bits layout.
+template <int T>
+__device__ __forceinline__ int slot_cell(int tid, int s, int H) { return tid + T * (s >> 1) + (s & 1) * H; }
+
+template <int T, int NB>
+__device__ __forceinline__ uint32_t valid_slots(int tid, const DevCfg& c) {
+    uint32_t m = 0;
+#pragma unroll
+    for (int s = 0; s < 2 * NB; ++s) {
+        const int b = tid + T * (s >> 1);
+        const int cell = b + (s & 1) * c.H;
+        if (b < c.H && cell < c.G2) m |= 1u << s;
+    }
+    return m;
+}
+
+// mant[s] = 23-bit mantissa of jax.random.uniform(key, (G*G,))[cell(s)]  (env.py:54,78)
+template <int T, int NB>
+__device__ __forceinline__ void noise_mantissas(int tid, const DevCfg& c, uint32_t k0, uint32_t k1, uint32_t (&mant)[2 * NB]) {
+#pragma unroll
+    for (int t = 0; t < NB; ++t) {
+        const int b = tid + T * t;
+        uint32_t o0 = 0, o1 = 0;
+        if (b < c.H) {
+            const int hi = c.H + b;
+            drl_threefry2x32(k0, k1, (uint32_t)b, hi < c.G2 ? (uint32_t)hi : 0u, o0, o1);
+        }
+        mant[2 * t] = o0 >> 9;
+        mant[2 * t + 1] = o1 >> 9;
+    }
+}
+
+// new_key, sub_key = split(key): two blocks hashed on even/odd lanes, exchanged by shuffle.
+__device__ __forceinline__ void split_warp(uint32_t& k0, uint32_t& k1, uint32_t& s0, uint32_t& s1) {
+    const uint32_t l = threadIdx.x & 1;
+    uint32_t a, b;
+    drl_threefry2x32(k0, k1, l, l + 2u, a, b);
+    k0 = __shfl_sync(FULL, a, 0);
+    k1 = __shfl_sync(FULL, a, 1);
+    s0 = __shfl_sync(FULL, b, 0);
+    s1 = __shfl_sync(FULL, b, 1);
+}
+
+// Positions of jax.lax.top_k(log(cand) + noise, k)[0 .. J_end) in rank order.  Key of a cell =
+// (cand ? mantissa + 1 : 0, G2 - cell): candidates by noise descending, ties and the -inf tail
+// (non-candidates) by ascending cell index -- XLA:CPU's total order with index tie-break.
+template <int T, int NB, class F>
+__device__ __forceinline__ void extract_ranks(Group<T>& grp, int tid, const DevCfg& c, const uint32_t (&mant)[2 * NB],
+                                              uint32_t candm, uint32_t validm, int J_end, F&& on_pos) {
+    uint32_t live = validm;
+    for (int j = 0; j < J_end; ++j) {
+        uint32_t bh = 0, bl = 0;
+        int bs = -1;
+#pragma unroll
+        for (int s = 0; s < 2 * NB; ++s) {
+            if ((live >> s) & 1u) {
+                const uint32_t hi = ((candm >> s) & 1u) ? mant[s] + 1u : 0u;
+                const uint32_t lo = (uint32_t)(c.G2 - slot_cell<T>(tid, s, c.H));
+                if (hi > bh || (hi == bh && lo > bl)) { bh = hi; bl = lo; bs = s; }
+            }
+        }
+        uint32_t mh, ml;
+        grp.max_pair(bh, bl, mh, ml);
+        if (bs >= 0 && bh == mh && bl == ml) live &= ~(1u << bs);
+        on_pos(j, c.G2 - (int)ml);
+    }
+}
+
+// ---- TMA bulk store of an obs tile ------------------------------------------------------------
+
+__device__ __forceinline__ void tile_wait_reusable(int lane) {
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+    __syncwarp();
+}
+
+__device__ __forceinline__ void tile_drain(int lane) {
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    __syncwarp();
+}
+
+__device__ __forceinline__ void tile_store(float* gdst, const float* ssrc, int bytes, int lane) {
+    const bool bulk = ((((unsigned long long)gdst) | (unsigned)bytes) & 15ull) == 0ull;
+    if (bulk) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) {
+            const uint32_t saddr = (uint32_t)__cvta_generic_to_shared(ssrc);
+            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(saddr), "r"(bytes)
+                         : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+    } else {   // env blocks that are only 8-byte aligned (odd n_drones): coalesced 64-bit stores
+        __syncwarp();
+        const float2* s2 = reinterpret_cast<const float2*>(ssrc);
+        float2* g2 = reinterpret_cast<float2*>(gdst);
+        for (int i = lane; i < (bytes >> 3); i += 32) g2[i] = s2[i];
+        __syncwarp();
+    }
+}
+
+// Compose the windows of drones [d0, d1) of the env staged in ``sm`` into ``tile`` (warp-level).
+// get_obs, env.py:274-309: channels 0 drone present, 1 packet (| carrying at the centre),
+// 2 dropzone, 3 station, 4 charge/100 at drone cells, 5 skyscraper or outside the grid.
+__device__ __forceinline__ void compose_tile(const DevCfg& c, const Smem& sm, int d0, int d1, float* tile, int lane) {
+    const int cells = (d1 - d0) * c.W2;
+    for (int ci = lane; ci < cells; ci += 32) {
+        const int dd = (int)fdiv((uint32_t)ci, c.W2, c.mulW2);
+        const int rem = ci - dd * c.W2;
+        const int wy = (int)fdiv((uint32_t)rem, c.W, c.mulW);
+        const int wx = rem - wy * c.W;
+        const uint32_t rec = sm.sdr[d0 + dd];
+        const int gx = (int)(rec & 0xFFu) + wx - c.r;
+        const int gy = (int)((rec >> 8) & 0xFFu) + wy - c.r;
+        int g = SKY, cd = 0;
+        if ((unsigned)gx < (unsigned)c.G && (unsigned)gy < (unsigned)c.G) {
+            const int idx = gy * c.G + gx;
+            g = sm.sg[idx];
+            cd = sm.code[idx];
+        }
+        const bool carry_here = (rem == c.center) && ((rec >> 16) & 1u);
+        float2 v01, v23, v45;
+        v01.x = cd > 0 ? 1.0f : 0.0f;
+        v01.y = (g == PACKET || carry_here) ? 1.0f : 0.0f;
+        v23.x = g == DROPZONE ? 1.0f : 0.0f;
+        v23.y = g == STATION ? 1.0f : 0.0f;
+        v45.x = cd > 0 ? sm.sdf[cd - 1] : 0.0f;
+        v45.y = g == SKY ? 1.0f : 0.0f;
+        float2* o = reinterpret_cast<float2*>(tile + ci * 6);
+        o[0] = v01;
+        o[1] = v23;
+        o[2] = v45;
+    }
+}
+
+// Publish final drone records for obs: sdr/sdf, and code[y*G+x] = drone index + 1 (padded_charge
+// scatter of env.py:282-283; with duplicate cells the highest drone index wins, as XLA:CPU does).
+__device__ __forceinline__ void obs_publish(const DevCfg& c, const Smem& sm, int lane, uint32_t rec, int& mark_cell) {
+    const bool isd = lane < c.n;
+    const int x = rec & 0xFFu, y = (rec >> 8) & 0xFFu, ch = rec >> 24;
+    const int cell = y * c.G + x;
+    const uint32_t grp = __match_any_sync(FULL, isd ? (uint32_t)cell : (0x80000000u | (uint32_t)lane));
+    mark_cell = -1;
+    if (isd) {
+        sm.sdr[lane] = rec;
+        sm.sdf[lane] = __fdiv_rn((float)ch, 100.0f);
+        if ((31 - __clz(grp)) == lane) { sm.code[cell] = (uint8_t)(lane + 1); mark_cell = cell; }
+    }
+}
+
+// Warp-level: compose + store every tile t = first, first + step, ... of env ``e``.
+__device__ __forceinline__ void obs_tiles(const DevCfg& c, const Smem& sm, float* obs, long long e, float* tile,
+                                          int first, int step, int lane) {
+    const int ntiles = (c.n + c.tile_drones - 1) / c.tile_drones;
+    for (int t = first; t < ntiles; t += step) {
+        const int d0 = t * c.tile_drones;
+        const int d1 = min(c.n, d0 + c.tile_drones);
+        tile_wait_reusable(lane);
+        compose_tile(c, sm, d0, d1, tile, lane);
+        float* gdst = obs + ((size_t)e * c.n + d0) * (size_t)(c.W2 * 6);
+        tile_store(gdst, tile, (d1 - d0) * c.W2 * 24, lane);
+    }
+}
+
+// ---- one env step on the state staged in shared memory ---------------------------------------
+//
+// Preconditions: sm.sg holds the env's ground, sm.code is all zero, group is synchronised.
+// Drone i lives in lane i of warp 0 of the group (``rec``/``act`` valid there).
+// Postconditions: sm.sg holds the new ground, ``rec`` the new drone record, rewards/dones written.
+template <int T, int NB>
+__device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const Smem& sm, uint32_t& rec, int act,
+                                         uint32_t k0, uint32_t k1, float* rewards_e, uint8_t* dones_e, Stats& st) {
+    constexpr bool kWarp = Group<T>::kWarp;
+    const int tid = Group<T>::tid();
+    const int lane = threadIdx.x & 31;
+    const bool drone_warp = kWarp || threadIdx.x < 32;
+    const int G = c.G, G2 = c.G2, n = c.n;
+
+    // cells this thread owns (noise layout) and which of them held a skyscraper BEFORE the step
+    const uint32_t validm = valid_slots<T, NB>(tid, c);
+    uint32_t oldsky = 0;
+#pragma unroll
+    for (int s = 0; s < 2 * NB; ++s)
+        if (((validm >> s) & 1u) && sm.sg[slot_cell<T>(tid, s, c.H)] == SKY) oldsky |= 1u << s;
+
+    uint32_t mP = 0, mD = 0, mDone = 0;
+    int x = 0, y = 0, carry = 0, ch = 0, tcell = 0;
+    bool done = false, surv = false, del_clear = false;
+
+    if (drone_warp) {
+        const bool isd = lane < n;
+        x = rec & 0xFFu; y = (rec >> 8) & 0xFFu;
+        const bool carry_old = (rec >> 16) & 1u;
+        ch = rec >> 24;
+        // S1 move, S2 off-board, S3 skyscraper (env.py:145-156)
+        const int nx = x + (act == A_RIGHT) - (act == A_LEFT);
+        const int ny = y + (act == A_DOWN) - (act == A_UP);
+        const bool off = (unsigned)nx >= (unsigned)G || (unsigned)ny >= (unsigned)G;
+        const int cell = (isd && !off) ? sm.sg[ny * G + nx] : 0;
+        const bool sky = cell == SKY;
+        // S4 drone/drone collisions (env.py:159-166): identical targets; off-board drones are collided anyway
+        const uint32_t pk = (isd && !off) ? (uint32_t)(ny * G + nx) : (0x80000000u | (uint32_t)lane);
+        const bool coll = __popc(__match_any_sync(FULL, pk)) > 1;
+        const bool collided = off | sky | coll;
+        // S5 charge (env.py:170-181)
+        const bool charging = (cell == STATION) && !collided;
+        const bool discharging = !charging && !collided;
+        int cc = ch;
+        cc = min(max(cc + (charging ? c.charge : 0), 0), 100);
+        cc = min(max(cc - (discharging ? c.discharge : 0), 0), 100);
+        done = isd && (collided || cc == 0);
+        surv = isd && !done;
+        ch = done ? 100 : cc;
+        // S6 pickup, S7 delivery (env.py:184-194)
+        const bool picked = (cell == PACKET) && surv && !carry_old;
+        const bool delivered = (cell == DROPZONE) && surv && carry_old;
+        carry = ((carry_old && surv) || picked) && !delivered;
+        // mask.at[new_y, new_x].set(v) (env.py:186,210): -1 wraps to G-1, >= G is dropped, and among
+        // drones hitting one cell the LAST update wins (sequential scatter on XLA:CPU)
+        const int ty = ny < 0 ? G - 1 : ny, tx = nx < 0 ? G - 1 : nx;
+        const bool tvalid = isd && ty < G && tx < G;
+        tcell = ty * G + tx;
+        const uint32_t tg = __match_any_sync(FULL, tvalid ? (uint32_t)tcell : (0x80000000u | (uint32_t)lane));
+        const bool last = (31 - __clz(tg)) == lane;
+        const bool pick_clear = tvalid && last && picked;
+        del_clear = tvalid && last && delivered;
+        mP = __ballot_sync(FULL, isd && (delivered || (done && carry_old)));   // env.py:201-202
+        mD = __ballot_sync(FULL, delivered);                                    // env.py:208
+        mDone = __ballot_sync(FULL, done);
+        if (pick_clear) sm.sg[tcell] = 0;
+        x = nx; y = ny;
+        if (isd) {
+            // S10 rewards (env.py:215-219): fp32, this order, no contraction
+            float rw = 0.0f;
+            rw = __fadd_rn(rw, __fmul_rn(c.rw_crash, done ? 1.0f : 0.0f));
+            rw = __fadd_rn(rw, __fmul_rn(c.rw_pickup, picked ? 1.0f : 0.0f));
+            rw = __fadd_rn(rw, __fmul_rn(c.rw_delivery, delivered ? 1.0f : 0.0f));
+            rw = __fadd_rn(rw, __fmul_rn(c.rw_charge, charging ? 1.0f : 0.0f));
+            rewards_e[lane] = rw;
+            dones_e[lane] = done ? 1 : 0;
+            st.dones += done; st.crashes += collided; st.pickups += picked; st.deliveries += delivered;
+            st.charging += charging;
+        }
+        if (!kWarp && lane == 0) { sm.misc[0] = mP; sm.misc[1] = mD; sm.misc[2] = mDone; }
+    }
+    Group<T>::sync();
+    if (!kWarp) { mP = sm.misc[0]; mD = sm.misc[1]; mDone = sm.misc[2]; }
+
+    // S8 packet respawn (env.py:197-203)
+    const int k = c.k_spawn;
+    uint32_t freem = 0;
+    int fc = 0;
+#pragma unroll
+    for (int s = 0; s < 2 * NB; ++s)
+        if (((validm >> s) & 1u) && sm.sg[slot_cell<T>(tid, s, c.H)] == 0) { freem |= 1u << s; ++fc; }
+    const int F1 = grp.sum(fc);
+
+    bool have_split = false, have_noise = false;
+    uint32_t sk0 = 0, sk1 = 0;
+    uint32_t mant[2 * NB];
+    auto ensure_noise = [&]() {
+        if (!have_split) { split_warp(k0, k1, sk0, sk1); have_split = true; }   // key, spawn_key = split(key)
+        if (!have_noise) { noise_mantissas<T, NB>(tid, c, sk0, sk1, mant); have_noise = true; }
+    };
+
+    if (mP != 0 || F1 < k) {
+        ensure_noise();
+        const int J = F1 < k ? k : 32 - __clz(mP);
+        extract_ranks<T, NB>(grp, tid, c, mant, freem, validm, J, [&](int j, int pos) {
+            if (tid == 0) sm.sg[pos] = (j < n && ((mP >> j) & 1u)) ? PACKET : 0;
+        });
+    }
+    // S9 dropzone respawn (env.py:205-212): same spawn_key, hence the same noise
+    if (mD != 0) {
+        Group<T>::sync();                                   // mask zeroing comes after the packet spawn's writes
+        if (drone_warp && del_clear) sm.sg[tcell] = 0;
+    }
+    if (mD != 0 || F1 - __popc(mP) < k) {
+        Group<T>::sync();
+        freem = 0; fc = 0;
+#pragma unroll
+        for (int s = 0; s < 2 * NB; ++s)
+            if (((validm >> s) & 1u) && sm.sg[slot_cell<T>(tid, s, c.H)] == 0) { freem |= 1u << s; ++fc; }
+        const int F2 = grp.sum(fc);
+        if (mD != 0 || F2 < k) {
+            ensure_noise();
+            const int J = F2 < k ? k : 32 - __clz(mD);
+            extract_ranks<T, NB>(grp, tid, c, mant, freem, validm, J, [&](int j, int pos) {
+                if (tid == 0) sm.sg[pos] = (j < n && ((mD >> j) & 1u)) ? DROPZONE : 0;
+            });
+        }
+    }
+
+    // S11 respawn of done drones (env.py:222-230) and S12 pickup on respawn (env.py:233-241)
+    if (mDone != 0) {
+        if (!have_split) { split_warp(k0, k1, sk0, sk1); have_split = true; }
+        split_warp(k0, k1, sk0, sk1);                      // key, spawn_key = split(key)  (second split)
+        // p_choice[x, y] = False for survivors (row = x), [-1, -1] -> last cell; &= ~(old ground == SKY)
+        if (drone_warp && surv) sm.code[x * G + y] = 1;
+        Group<T>::sync();                                   // also orders the ground writes above
+        uint32_t candm = 0;
+#pragma unroll
+        for (int s = 0; s < 2 * NB; ++s) {
+            const int cell = slot_cell<T>(tid, s, c.H);
+            if (((validm >> s) & 1u) && !((oldsky >> s) & 1u) && cell != G2 - 1 && sm.code[cell] == 0) candm |= 1u << s;
+        }
+        noise_mantissas<T, NB>(tid, c, sk0, sk1, mant);
+        extract_ranks<T, NB>(grp, tid, c, mant, candm, validm, 32 - __clz(mDone), [&](int j, int pos) {
+            if (drone_warp && lane == j && done) {
+                x = (int)fdiv((uint32_t)pos, G, c.mulG);    // rank i -> drone i: x = pos // G, y = pos % G
+                y = pos - x * G;
+                if (sm.sg[pos] == PACKET) {                 // package_mask[new_x, new_y]: flat index x*G+y == pos
+                    carry = 1;
+                    sm.sg[pos] = 0;
+                    st.respawn_pickups += 1;
+                }
+            }
+        });
+        if (drone_warp && surv) sm.code[x * G + y] = 0;     // restore the all-zero invariant
+    }
+    if (drone_warp)
+        rec = (uint32_t)x | ((uint32_t)y << 8) | ((uint32_t)carry << 16) | ((uint32_t)ch << 24);
+    Group<T>::sync();
+}
+
+// ---- one env reset (env.py:89-135) -------------------------------------------------------------
+template <int T, int NB>
+__device__ __forceinline__ void env_reset(Group<T>& grp, const DevCfg& c, const Smem& sm, uint32_t& rec, uint32_t k0,
+                                          uint32_t k1) {
+    constexpr bool kWarp = Group<T>::kWarp;
+    const int tid = Group<T>::tid();
+    const int lane = threadIdx.x & 31;
+    const bool drone_warp = kWarp || threadIdx.x < 32;
+    const int G = c.G, G2 = c.G2, n = c.n;
+    const uint32_t validm = valid_slots<T, NB>(tid, c);
+    uint32_t mant[2 * NB];
+    uint32_t sk0, sk1;
+    const int objs[4] = {PACKET, DROPZONE, STATION, SKY};
+    // ground = zeros (the caller cleared sm.sg); four spawns, each on the grid so far (env.py:106-114)
+#pragma unroll 1
+    for (int t = 0; t < 4; ++t) {
+        split_warp(k0, k1, sk0, sk1);
+        uint32_t freem = 0;
+#pragma unroll
+        for (int s = 0; s < 2 * NB; ++s)
+            if (((validm >> s) & 1u) && sm.sg[slot_cell<T>(tid, s, c.H)] == 0) freem |= 1u << s;
+        noise_mantissas<T, NB>(tid, c, sk0, sk1, mant);
+        const int obj = objs[t];
+        extract_ranks<T, NB>(grp, tid, c, mant, freem, validm, c.k_reset[t], [&](int, int pos) {
+            if (tid == 0) sm.sg[pos] = (uint8_t)obj;
+        });
+        Group<T>::sync();
+    }
+    // spawn_air with every drone at -1 and exclude = (ground == SKY) in [x, y] indexing (env.py:116-119)
+    split_warp(k0, k1, sk0, sk1);
+    uint32_t candm = 0;
+#pragma unroll
+    for (int s = 0; s < 2 * NB; ++s) {
+        const int cell = slot_cell<T>(tid, s, c.H);
+        if (((validm >> s) & 1u) && cell != G2 - 1 && sm.sg[cell] != SKY) candm |= 1u << s;
+    }
+    noise_mantissas<T, NB>(tid, c, sk0, sk1, mant);
+    int x = 0, y = 0;
+    extract_ranks<T, NB>(grp, tid, c, mant, candm, validm, n, [&](int j, int pos) {
+        if (drone_warp && lane == j) {
+            x = (int)fdiv((uint32_t)pos, G, c.mulG);
+            y = pos - x * G;
+        }
+    });
+    // carrying = ground[air_y, air_x] == PACKET, then remove those packets (env.py:122-127)
+    if (drone_warp) {
+        int carry = 0;
+        if (lane < n && sm.sg[y * G + x] == PACKET) { carry = 1; sm.sg[y * G + x] = 0; }
+        rec = (uint32_t)x | ((uint32_t)y << 8) | ((uint32_t)carry << 16) | (100u << 24);
+    }
+    Group<T>::sync();
+}
+
+}  // namespace drl

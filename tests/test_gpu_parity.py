@@ -1,0 +1,108 @@
+"""CUDA env vs the C oracle, bit-exact: reset, multi-step rollouts with periodic resets, obs.
+
+Mirrors the parity run SURVEY.md 8(d) prescribes (same keys, same actions, every state tensor,
+rewards and dones every step, obs every few steps) at sizes the oracle finishes in seconds.
+"""
+import numpy as np
+import pytest
+import torch
+
+from helpers import oracle_params, assert_state_equal
+
+pytestmark = pytest.mark.gpu
+
+CONFIGS = [
+    # (grid, drones, radius, extra params, num_envs, steps)
+    (8, 3, 3, {}, 4096, 60),                     # DroneEnvParams defaults (warp mode, 1 block/lane, odd n)
+    (9, 4, 3, {}, 4096, 60),                     # train_jax.py CLI defaults (odd G*G -> padded counters)
+    (5, 2, 2, {'packets_factor': 2, 'dropzones_factor': 2, 'stations_factor': 2, 'skyscrapers_factor': 2}, 2048, 60),
+    (11, 7, 1, {}, 1024, 40),                    # largest warp-mode grid
+    (12, 6, 4, {}, 512, 40),                     # smallest CTA-mode grid
+    (6, 4, 3, {'packets_factor': 4, 'dropzones_factor': 2, 'stations_factor': 1, 'skyscrapers_factor': 1}, 2048, 80),
+    (4, 2, 2, {'packets_factor': 4, 'dropzones_factor': 2, 'stations_factor': 1, 'skyscrapers_factor': 1}, 2048, 80),   # free < k edge: top_k runs into occupied cells
+    (3, 3, 1, {'packets_factor': 1, 'dropzones_factor': 1, 'stations_factor': 0, 'skyscrapers_factor': 1}, 2048, 60),   # tiny: spawn_air runs out of candidates
+    (32, 16, 3, {}, 128, 30),
+    (64, 32, 5, {'stations_factor': 8, 'skyscrapers_factor': 16}, 24, 12),   # BASELINE large world
+]
+
+
+@pytest.mark.parametrize('G,n,r,extra,N,steps', CONFIGS)
+def test_rollout_matches_oracle(c_oracle, G, n, r, extra, N, steps):
+    import dronerl_b200 as drl
+    C = c_oracle
+    p = drl.DroneEnvParams(grid_size=G, n_drones=n, window_radius=r, **extra)
+    op = oracle_params(p)
+    env = drl.DeliveryDrones()
+    rng = np.random.default_rng(G * 1000 + n)
+    key0 = drl.random.PRNGKey(G * 7 + n)
+
+    reset_keys = C.split(key0, N)
+    state = env.reset(torch.from_numpy(reset_keys).cuda(), p)
+    ostate = C.reset(reset_keys, op)
+    assert_state_equal(state, ostate, 'after reset')
+    np.testing.assert_array_equal(env.get_obs(state, p).cpu().numpy(), C.get_obs(ostate, op))
+
+    for t in range(steps):
+        acts = rng.integers(0, 5, size=(N, n)).astype(np.int32)
+        keys = C.split(drl.random.PRNGKey(1000 + t), N)
+        with_obs = (t % 4 == 0)
+        out = env.step(torch.from_numpy(keys).cuda(), state, torch.from_numpy(acts).cuda(), p, return_obs=with_obs)
+        orew, odone = C.step(keys, ostate, acts, op)
+        assert_state_equal(out[0], ostate, f'step {t}')
+        np.testing.assert_array_equal(out[2].cpu().numpy(), odone, err_msg=f'dones step {t}')
+        r_cuda = out[1].cpu().numpy()
+        assert r_cuda.dtype == np.float32
+        np.testing.assert_array_equal(r_cuda.view(np.uint32), orew.view(np.uint32), err_msg=f'rewards step {t}')
+        if with_obs:
+            oobs = C.get_obs(ostate, op)
+            np.testing.assert_array_equal(out[3].cpu().numpy().view(np.uint32), oobs.view(np.uint32),
+                                          err_msg=f'fused obs step {t}')
+            np.testing.assert_array_equal(env.get_obs(state, p).cpu().numpy().view(np.uint32), oobs.view(np.uint32),
+                                          err_msg=f'standalone obs step {t}')
+        if t % 25 == 24:   # periodic reset as train_jax.py:101-113
+            rk = C.split(drl.random.PRNGKey(5000 + t), N)
+            state = env.reset(torch.from_numpy(rk).cuda(), p)
+            ostate = C.reset(rk, op)
+            assert_state_equal(state, ostate, f'reset at {t}')
+
+
+def test_parent_key_split_matches_explicit_keys(c_oracle):
+    """step(key(2,), ...) on a batched state == vmap(step)(split(key, N), ...)  (train_jax.py:52-54)."""
+    import dronerl_b200 as drl
+    C = c_oracle
+    p = drl.DroneEnvParams(grid_size=9, n_drones=4)
+    op = oracle_params(p)
+    env = drl.DeliveryDrones()
+    N = 1000
+    key = drl.random.PRNGKey(3)
+    state = env.reset(key, p, num_envs=N)
+    ostate = C.reset(C.split(key, N), op)
+    assert_state_equal(state, ostate, 'reset from parent key')
+    acts = np.random.default_rng(0).integers(0, 5, size=(N, 4)).astype(np.int32)
+    k2 = drl.random.PRNGKey(11)
+    state, rew, done = env.step(k2, state, acts, p)
+    orew, odone = C.step(C.split(k2, N), ostate, acts, op)
+    assert_state_equal(state, ostate, 'step from parent key')
+    np.testing.assert_array_equal(rew.cpu().numpy(), orew)
+    np.testing.assert_array_equal(done.cpu().numpy(), odone)
+
+
+def test_sharded_slices_equal_unsharded(c_oracle):
+    """Two slices addressed by global env index reproduce the unsharded run."""
+    import dronerl_b200 as drl
+    p = drl.DroneEnvParams(grid_size=9, n_drones=4)
+    env = drl.DeliveryDrones()
+    N = 1024
+    key = drl.random.PRNGKey(5)
+    full = env.reset(key, p, num_envs=N)
+    halves = [env.reset(key, p, num_envs=N // 2, env_offset=o, num_envs_global=N) for o in (0, N // 2)]
+    acts = torch.from_numpy(np.random.default_rng(1).integers(0, 5, size=(N, 4)).astype(np.int8)).cuda()
+    for t in range(10):
+        k = drl.random.PRNGKey(100 + t)
+        env.step(k, full, acts, p)
+        for i, h in enumerate(halves):
+            env.step(k, h, acts[i * N // 2:(i + 1) * N // 2], p)
+    got_g = torch.cat([h.ground_raw for h in halves]).cpu().numpy()
+    got_d = torch.cat([h.drones_raw for h in halves]).cpu().numpy()
+    np.testing.assert_array_equal(got_g, full.ground_raw.cpu().numpy())
+    np.testing.assert_array_equal(got_d, full.drones_raw.cpu().numpy())
