@@ -38,6 +38,12 @@ __device__ __forceinline__ void flush_stats(const Stats& st, unsigned env_steps,
     }
 }
 
+// number of zero bytes in 16 bytes of ground (free cells; row padding is zero too)
+__device__ __forceinline__ int zero_bytes(const uint4& v) {
+    return (__popc(__vcmpeq4(v.x, 0u)) + __popc(__vcmpeq4(v.y, 0u)) + __popc(__vcmpeq4(v.z, 0u)) +
+            __popc(__vcmpeq4(v.w, 0u))) >> 3;
+}
+
 __device__ __forceinline__ void zero_code(const DevCfg& c, const Smem& sm, int tid, int nthreads) {
     uint32_t* w = reinterpret_cast<uint32_t*>(sm.code);
     const int words = (c.off_sdr - c.off_code) >> 2;
@@ -63,6 +69,7 @@ k_step_warp(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint
     long long e = (long long)blockIdx.x * kWarpsPerBlock + warp;
     Stats st;
     unsigned env_steps = 0;
+    const uint32_t validm = valid_slots<32, NB>(lane, c);
 
     EnvInputs nxt = {};
     auto prefetch = [&](long long ee) {
@@ -82,18 +89,19 @@ k_step_warp(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint
         EnvInputs cur = nxt;
         prefetch(e + stride);
         __syncwarp();
-        if (lane < nvec) reinterpret_cast<uint4*>(sm.sg)[lane] = cur.gv;
-        __syncwarp();
-        env_step<32, NB>(grp, c, sm, cur.rec, cur.act, cur.k0, cur.k1, rewards + e * n, dones + e * n, st);
+        int zc = 0;
+        if (lane < nvec) {
+            reinterpret_cast<uint4*>(sm.sg)[lane] = cur.gv;
+            zc = zero_bytes(cur.gv);
+        }
+        const int F0 = (int)__reduce_add_sync(FULL, (unsigned)zc) - (c.GS - c.G2);   // also orders the stores above
+        env_step<32, NB>(grp, c, sm, validm, F0, cur.rec, cur.act, cur.k0, cur.k1, rewards + e * n, dones + e * n, st);
         if (lane < nvec) reinterpret_cast<uint4*>(ground + e * c.GS)[lane] = reinterpret_cast<const uint4*>(sm.sg)[lane];
         if (lane < n) drones[e * n + lane] = cur.rec;
         if (obs != nullptr) {
-            int mark;
-            obs_publish(c, sm, lane, cur.rec, mark);
+            obs_publish(c, sm, lane, cur.rec);
             __syncwarp();
             obs_tiles(c, sm, obs, e, tile, 0, 1, lane);
-            __syncwarp();
-            if (mark >= 0) sm.code[mark] = 0;
         }
         ++env_steps;
     }
@@ -142,12 +150,9 @@ k_obs_warp(const __grid_constant__ DevCfg c, const uint8_t* __restrict__ ground,
         __syncwarp();
         if (lane < nvec) reinterpret_cast<uint4*>(sm.sg)[lane] = reinterpret_cast<const uint4*>(ground + e * c.GS)[lane];
         const uint32_t rec = lane < n ? drones[e * n + lane] : 0u;
-        int mark;
-        obs_publish(c, sm, lane, rec, mark);
+        obs_publish(c, sm, lane, rec);
         __syncwarp();
         obs_tiles(c, sm, obs, e, tile, 0, 1, lane);
-        __syncwarp();
-        if (mark >= 0) sm.code[mark] = 0;
     }
     tile_drain(lane);
 }
@@ -169,9 +174,15 @@ k_step_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint3
     const int nvec = c.GS >> 4, n = c.n;
     Stats st;
     unsigned env_steps = 0;
+    const uint32_t validm = valid_slots<T, NB>(threadIdx.x, c);
+    __syncthreads();
     for (long long e = blockIdx.x; e < c.N; e += gridDim.x) {
-        for (int i = threadIdx.x; i < nvec; i += T)
-            reinterpret_cast<uint4*>(sm.sg)[i] = reinterpret_cast<const uint4*>(ground + e * c.GS)[i];
+        int zc = 0;
+        for (int i = threadIdx.x; i < nvec; i += T) {
+            const uint4 v = reinterpret_cast<const uint4*>(ground + e * c.GS)[i];
+            reinterpret_cast<uint4*>(sm.sg)[i] = v;
+            zc += zero_bytes(v);
+        }
         uint32_t rec = 0;
         int act = 4;
         if (threadIdx.x < n) {
@@ -179,18 +190,16 @@ k_step_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint3
             act = actions[e * n + threadIdx.x];
         }
         const uint2 kk = *reinterpret_cast<const uint2*>(keys + 2 * e);
-        __syncthreads();
-        env_step<T, NB>(grp, c, sm, rec, act, kk.x, kk.y, rewards + e * n, dones + e * n, st);
+        const int F0 = grp.sum(zc) - (c.GS - c.G2);     // block-wide: also publishes the ground stores
+        env_step<T, NB>(grp, c, sm, validm, F0, rec, act, kk.x, kk.y, rewards + e * n, dones + e * n, st);
         for (int i = threadIdx.x; i < nvec; i += T)
             reinterpret_cast<uint4*>(ground + e * c.GS)[i] = reinterpret_cast<const uint4*>(sm.sg)[i];
         if (threadIdx.x < n) drones[e * n + threadIdx.x] = rec;
         if (obs != nullptr) {
-            int mark = -1;
-            if (warp == 0) obs_publish(c, sm, lane, rec, mark);
+            if (warp == 0) obs_publish(c, sm, lane, rec);
             __syncthreads();
             obs_tiles(c, sm, obs, e, tile, warp, T / 32, lane);
             __syncthreads();
-            if (mark >= 0) sm.code[mark] = 0;
         }
         if (threadIdx.x == 0) ++env_steps;
     }
@@ -237,15 +246,12 @@ k_obs_cta(const __grid_constant__ DevCfg c, const uint8_t* __restrict__ ground, 
         __syncthreads();
         for (int i = threadIdx.x; i < nvec; i += T)
             reinterpret_cast<uint4*>(sm.sg)[i] = reinterpret_cast<const uint4*>(ground + e * c.GS)[i];
-        int mark = -1;
         if (warp == 0) {
             const uint32_t rec = lane < n ? drones[e * n + lane] : 0u;
-            obs_publish(c, sm, lane, rec, mark);
+            obs_publish(c, sm, lane, rec);
         }
         __syncthreads();
         obs_tiles(c, sm, obs, e, tile, warp, T / 32, lane);
-        __syncthreads();
-        if (mark >= 0) sm.code[mark] = 0;
     }
     tile_drain(lane);
 }
@@ -394,7 +400,7 @@ int drl_create(const drl_config* cfg, drl_env** out) {
     c.charge = cfg->charge; c.discharge = cfg->discharge;
     c.rw_pickup = cfg->pickup_reward; c.rw_delivery = cfg->delivery_reward;
     c.rw_crash = cfg->crash_reward; c.rw_charge = cfg->charge_reward;
-    c.mulG = magic(G); c.mulW = magic(c.W); c.mulW2 = magic(c.W2);
+    c.mulG = magic(G); c.mulW = magic(c.W); c.mulW2 = magic(c.W2); c.mulN = magic(n);
     c.N = cfg->num_envs;
 
     e->warp_mode = G2 <= 128;
@@ -408,6 +414,7 @@ int drl_create(const drl_config* cfg, drl_env** out) {
         e->nb = c.H <= 2 * kCtaThreads ? 2 : c.H <= 8 * kCtaThreads ? 8 : 16;
         c.tile_drones = (n >= 2 && 2 * cell_bytes <= 12288) ? 2 : 1;
     }
+    c.ntiles = (n + c.tile_drones - 1) / c.tile_drones;
     c.tile_stride = round_up(c.tile_drones * cell_bytes, 128);
     c.off_code = c.GS;
     c.off_sdr = c.off_code + round_up((int)G2, 16);

@@ -38,8 +38,8 @@ struct DevCfg {
     int k_reset[4];            // packets, dropzones, stations, skyscrapers counts in reset order
     int charge, discharge;
     float rw_pickup, rw_delivery, rw_crash, rw_charge;
-    uint32_t mulG, mulW, mulW2;  // magic multipliers: x / d == umulhi(x, mul) for x*d < 2^32
-    int tile_drones;           // drones per obs tile
+    uint32_t mulG, mulW, mulW2, mulN;  // magic multipliers: x / d == umulhi(x, mul) for x*d < 2^32
+    int tile_drones, ntiles;   // drones per obs tile, tiles per env
     int tile_stride;           // bytes reserved per obs tile buffer
     // shared-memory carve-up (bytes from the group's base)
     int off_code, off_sdr, off_sdf, off_misc, off_red, off_tile;
@@ -167,22 +167,41 @@ __device__ __forceinline__ void split_warp(uint32_t& k0, uint32_t& k1, uint32_t&
 template <int T, int NB, class F>
 __device__ __forceinline__ void extract_ranks(Group<T>& grp, int tid, const DevCfg& c, const uint32_t (&mant)[2 * NB],
                                               uint32_t candm, uint32_t validm, int J_end, F&& on_pos) {
-    uint32_t live = validm;
-    for (int j = 0; j < J_end; ++j) {
-        uint32_t bh = 0, bl = 0;
-        int bs = -1;
+    if constexpr (T == 32) {
+        // warp mode: G2 <= 128, so (mantissa + 1) << 8 | (G2 - cell) fits one 32-bit key per slot
+        uint32_t key[2 * NB];
 #pragma unroll
         for (int s = 0; s < 2 * NB; ++s) {
-            if ((live >> s) & 1u) {
-                const uint32_t hi = ((candm >> s) & 1u) ? mant[s] + 1u : 0u;
-                const uint32_t lo = (uint32_t)(c.G2 - slot_cell<T>(tid, s, c.H));
-                if (hi > bh || (hi == bh && lo > bl)) { bh = hi; bl = lo; bs = s; }
-            }
+            const uint32_t hi = ((candm >> s) & 1u) ? mant[s] + 1u : 0u;
+            key[s] = ((validm >> s) & 1u) ? ((hi << 8) | (uint32_t)(c.G2 - slot_cell<T>(tid, s, c.H))) : 0u;
         }
-        uint32_t mh, ml;
-        grp.max_pair(bh, bl, mh, ml);
-        if (bs >= 0 && bh == mh && bl == ml) live &= ~(1u << bs);
-        on_pos(j, c.G2 - (int)ml);
+        for (int j = 0; j < J_end; ++j) {
+            uint32_t b = key[0];
+#pragma unroll
+            for (int s = 1; s < 2 * NB; ++s) b = max(b, key[s]);
+            const uint32_t m = __reduce_max_sync(FULL, b);
+#pragma unroll
+            for (int s = 0; s < 2 * NB; ++s) key[s] = key[s] == m ? 0u : key[s];
+            on_pos(j, c.G2 - (int)(m & 0xFFu));
+        }
+    } else {
+        uint32_t live = validm;
+        for (int j = 0; j < J_end; ++j) {
+            uint32_t bh = 0, bl = 0;
+            int bs = -1;
+#pragma unroll
+            for (int s = 0; s < 2 * NB; ++s) {
+                if ((live >> s) & 1u) {
+                    const uint32_t hi = ((candm >> s) & 1u) ? mant[s] + 1u : 0u;
+                    const uint32_t lo = (uint32_t)(c.G2 - slot_cell<T>(tid, s, c.H));
+                    if (hi > bh || (hi == bh && lo > bl)) { bh = hi; bl = lo; bs = s; }
+                }
+            }
+            uint32_t mh, ml;
+            grp.max_pair(bh, bl, mh, ml);
+            if (bs >= 0 && bh == mh && bl == ml) live &= ~(1u << bs);
+            on_pos(j, c.G2 - (int)ml);
+        }
     }
 }
 
@@ -221,57 +240,74 @@ __device__ __forceinline__ void tile_store(float* gdst, const float* ssrc, int b
 // Compose the windows of drones [d0, d1) of the env staged in ``sm`` into ``tile`` (warp-level).
 // get_obs, env.py:274-309: channels 0 drone present, 1 packet (| carrying at the centre),
 // 2 dropzone, 3 station, 4 charge/100 at drone cells, 5 skyscraper or outside the grid.
+// The one-hot tensor is ~90 % zeros, so the tile is zero-filled with 128-bit stores and only the
+// non-zero entries are scattered: one lane per window ROW walks its W cells (ground class -> one
+// store), then one lane per (viewer, other drone) pair marks channels 0 and 4.
 __device__ __forceinline__ void compose_tile(const DevCfg& c, const Smem& sm, int d0, int d1, float* tile, int lane) {
-    const int cells = (d1 - d0) * c.W2;
-    for (int ci = lane; ci < cells; ci += 32) {
-        const int dd = (int)fdiv((uint32_t)ci, c.W2, c.mulW2);
-        const int rem = ci - dd * c.W2;
-        const int wy = (int)fdiv((uint32_t)rem, c.W, c.mulW);
-        const int wx = rem - wy * c.W;
+    const int nd = d1 - d0;
+    const int vecs = (nd * c.W2 * 24 + 15) >> 4;          // tile buffers are padded to 128 B
+    float4* t4 = reinterpret_cast<float4*>(tile);
+    for (int i = lane; i < vecs; i += 32) t4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    __syncwarp();
+    // ground value -> channel: 0 -> none, SKY 2 -> 5, STATION 3 -> 3, DROPZONE 4 -> 2, PACKET 5 -> 1
+    constexpr uint32_t kChan = (5u << 8) | (3u << 12) | (2u << 16) | (1u << 20);
+    const int rows = nd * c.W;
+    for (int row = lane; row < rows; row += 32) {
+        const int dd = (int)fdiv((uint32_t)row, c.W, c.mulW);
+        const int wy = row - dd * c.W;
         const uint32_t rec = sm.sdr[d0 + dd];
-        const int gx = (int)(rec & 0xFFu) + wx - c.r;
         const int gy = (int)((rec >> 8) & 0xFFu) + wy - c.r;
-        int g = SKY, cd = 0;
-        if ((unsigned)gx < (unsigned)c.G && (unsigned)gy < (unsigned)c.G) {
-            const int idx = gy * c.G + gx;
-            g = sm.sg[idx];
-            cd = sm.code[idx];
+        int gx = (int)(rec & 0xFFu) - c.r;
+        float* o = tile + row * c.W * 6;
+        if ((unsigned)gy >= (unsigned)c.G) {
+            for (int wx = 0; wx < c.W; ++wx) o[wx * 6 + 5] = 1.0f;          // the whole row is wall
+        } else {
+            const uint8_t* grow = sm.sg + gy * c.G;
+            for (int wx = 0; wx < c.W; ++wx, ++gx) {
+                const uint32_t g = (unsigned)gx < (unsigned)c.G ? grow[gx] : (uint32_t)SKY;
+                const uint32_t ch = (kChan >> (4u * g)) & 7u;
+                if (ch) o[wx * 6 + ch] = 1.0f;
+            }
         }
-        const bool carry_here = (rem == c.center) && ((rec >> 16) & 1u);
-        float2 v01, v23, v45;
-        v01.x = cd > 0 ? 1.0f : 0.0f;
-        v01.y = (g == PACKET || carry_here) ? 1.0f : 0.0f;
-        v23.x = g == DROPZONE ? 1.0f : 0.0f;
-        v23.y = g == STATION ? 1.0f : 0.0f;
-        v45.x = cd > 0 ? sm.sdf[cd - 1] : 0.0f;
-        v45.y = g == SKY ? 1.0f : 0.0f;
-        float2* o = reinterpret_cast<float2*>(tile + ci * 6);
-        o[0] = v01;
-        o[1] = v23;
-        o[2] = v45;
     }
+    // drones: obs[d, wy, wx, 0] = 1 and [.., 4] = charge/100 where another (or the same) drone sits in
+    // the window; with several drones in one cell the highest index provides the charge (bit 17 of sdr)
+    const int pairs = nd * c.n;
+    for (int pi = lane; pi < pairs; pi += 32) {
+        const int dd = (int)fdiv((uint32_t)pi, c.n, c.mulN);
+        const int j = pi - dd * c.n;
+        const uint32_t rv = sm.sdr[d0 + dd], rj = sm.sdr[j];
+        const int dx = (int)(rj & 0xFFu) - (int)(rv & 0xFFu) + c.r;
+        const int dy = (int)((rj >> 8) & 0xFFu) - (int)((rv >> 8) & 0xFFu) + c.r;
+        if (((rj >> 17) & 1u) && (unsigned)dx < (unsigned)c.W && (unsigned)dy < (unsigned)c.W) {
+            float* o = tile + ((dd * c.W2 + dy * c.W + dx) * 6);
+            o[0] = 1.0f;
+            o[4] = sm.sdf[j];
+        }
+    }
+    // obs[:, r, r, 1] |= carrying_package
+    if (lane < nd && ((sm.sdr[d0 + lane] >> 16) & 1u)) tile[(lane * c.W2 + c.center) * 6 + 1] = 1.0f;
+    for (int d = lane + 32; d < nd; d += 32)
+        if ((sm.sdr[d0 + d] >> 16) & 1u) tile[(d * c.W2 + c.center) * 6 + 1] = 1.0f;
 }
 
-// Publish final drone records for obs: sdr/sdf, and code[y*G+x] = drone index + 1 (padded_charge
-// scatter of env.py:282-283; with duplicate cells the highest drone index wins, as XLA:CPU does).
-__device__ __forceinline__ void obs_publish(const DevCfg& c, const Smem& sm, int lane, uint32_t rec, int& mark_cell) {
+// Publish final drone records for obs: sdr[i] = record | (owns-its-cell << 17), sdf[i] = charge/100.
+// "Owns" = highest drone index in that cell: the padded_charge scatter of env.py:282-283 is applied
+// in drone order on XLA:CPU, so the last drone's charge is the one that shows.
+__device__ __forceinline__ void obs_publish(const DevCfg& c, const Smem& sm, int lane, uint32_t rec) {
     const bool isd = lane < c.n;
-    const int x = rec & 0xFFu, y = (rec >> 8) & 0xFFu, ch = rec >> 24;
-    const int cell = y * c.G + x;
-    const uint32_t grp = __match_any_sync(FULL, isd ? (uint32_t)cell : (0x80000000u | (uint32_t)lane));
-    mark_cell = -1;
+    const uint32_t grp = __match_any_sync(FULL, isd ? (rec & 0xFFFFu) : (0x80000000u | (uint32_t)lane));
     if (isd) {
-        sm.sdr[lane] = rec;
-        sm.sdf[lane] = __fdiv_rn((float)ch, 100.0f);
-        if ((31 - __clz(grp)) == lane) { sm.code[cell] = (uint8_t)(lane + 1); mark_cell = cell; }
+        const bool owner = (31 - __clz(grp)) == lane;
+        sm.sdr[lane] = (rec & 0xFF01FFFFu) | (owner ? (1u << 17) : 0u);
+        sm.sdf[lane] = __fdiv_rn((float)(rec >> 24), 100.0f);
     }
 }
 
 // Warp-level: compose + store every tile t = first, first + step, ... of env ``e``.
 __device__ __forceinline__ void obs_tiles(const DevCfg& c, const Smem& sm, float* obs, long long e, float* tile,
                                           int first, int step, int lane) {
-    const int ntiles = (c.n + c.tile_drones - 1) / c.tile_drones;
-    for (int t = first; t < ntiles; t += step) {
+    for (int t = first; t < c.ntiles; t += step) {
         const int d0 = t * c.tile_drones;
         const int d1 = min(c.n, d0 + c.tile_drones);
         tile_wait_reusable(lane);
@@ -283,27 +319,36 @@ __device__ __forceinline__ void obs_tiles(const DevCfg& c, const Smem& sm, float
 
 // ---- one env step on the state staged in shared memory ---------------------------------------
 //
-// Preconditions: sm.sg holds the env's ground, sm.code is all zero, group is synchronised.
+// Preconditions: sm.sg holds the env's ground, sm.code is all zero, group is synchronised;
+// ``validm`` = valid_slots() of this thread, ``F0`` = number of free (zero) cells of that ground.
 // Drone i lives in lane i of warp 0 of the group (``rec``/``act`` valid there).
 // Postconditions: sm.sg holds the new ground, ``rec`` the new drone record, rewards/dones written.
 template <int T, int NB>
-__device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const Smem& sm, uint32_t& rec, int act,
-                                         uint32_t k0, uint32_t k1, float* rewards_e, uint8_t* dones_e, Stats& st) {
+__device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const Smem& sm, uint32_t validm, int F0,
+                                         uint32_t& rec, int act, uint32_t k0, uint32_t k1, float* rewards_e,
+                                         uint8_t* dones_e, Stats& st) {
     constexpr bool kWarp = Group<T>::kWarp;
     const int tid = Group<T>::tid();
     const int lane = threadIdx.x & 31;
     const bool drone_warp = kWarp || threadIdx.x < 32;
     const int G = c.G, G2 = c.G2, n = c.n;
 
-    // cells this thread owns (noise layout) and which of them held a skyscraper BEFORE the step
-    const uint32_t validm = valid_slots<T, NB>(tid, c);
+    // Which owned cells held a skyscraper BEFORE the step (spawn_air's exclude mask).  Skyscrapers only
+    // ever change when a spawn runs out of free cells (the erasing-zeros edge), so the mask is captured
+    // lazily: right before such an edge, or else at respawn time from the unchanged cells.
     uint32_t oldsky = 0;
+    bool have_oldsky = false;
+    auto capture_oldsky = [&]() {
+        if (!have_oldsky) {
 #pragma unroll
-    for (int s = 0; s < 2 * NB; ++s)
-        if (((validm >> s) & 1u) && sm.sg[slot_cell<T>(tid, s, c.H)] == SKY) oldsky |= 1u << s;
+            for (int s = 0; s < 2 * NB; ++s)
+                if (((validm >> s) & 1u) && sm.sg[slot_cell<T>(tid, s, c.H)] == SKY) oldsky |= 1u << s;
+            have_oldsky = true;
+        }
+    };
 
     uint32_t mP = 0, mD = 0, mDone = 0;
-    int x = 0, y = 0, carry = 0, ch = 0, tcell = 0;
+    int x = 0, y = 0, carry = 0, ch = 0, tcell = 0, npick = 0;
     bool done = false, surv = false, del_clear = false;
 
     if (drone_warp) {
@@ -360,19 +405,26 @@ __device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const S
             st.dones += done; st.crashes += collided; st.pickups += picked; st.deliveries += delivered;
             st.charging += charging;
         }
-        if (!kWarp && lane == 0) { sm.misc[0] = mP; sm.misc[1] = mD; sm.misc[2] = mDone; }
+        npick = __popc(__ballot_sync(FULL, pick_clear));
+        if (!kWarp && lane == 0) { sm.misc[0] = mP; sm.misc[1] = mD; sm.misc[2] = mDone; sm.misc[3] = (uint32_t)npick; }
     }
-    Group<T>::sync();
-    if (!kWarp) { mP = sm.misc[0]; mD = sm.misc[1]; mDone = sm.misc[2]; }
+    if (!kWarp) {
+        Group<T>::sync();
+        mP = sm.misc[0]; mD = sm.misc[1]; mDone = sm.misc[2]; npick = (int)sm.misc[3];
+    }
 
-    // S8 packet respawn (env.py:197-203)
+    // S8 packet respawn (env.py:197-203).  Free cells now = free cells before + cells a pickup cleared.
     const int k = c.k_spawn;
+    const int F1 = F0 + npick;
     uint32_t freem = 0;
-    int fc = 0;
+    auto scan_free = [&]() {
+        int fc = 0;
+        freem = 0;
 #pragma unroll
-    for (int s = 0; s < 2 * NB; ++s)
-        if (((validm >> s) & 1u) && sm.sg[slot_cell<T>(tid, s, c.H)] == 0) { freem |= 1u << s; ++fc; }
-    const int F1 = grp.sum(fc);
+        for (int s = 0; s < 2 * NB; ++s)
+            if (((validm >> s) & 1u) && sm.sg[slot_cell<T>(tid, s, c.H)] == 0) { freem |= 1u << s; ++fc; }
+        return fc;
+    };
 
     bool have_split = false, have_noise = false;
     uint32_t sk0 = 0, sk1 = 0;
@@ -383,6 +435,9 @@ __device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const S
     };
 
     if (mP != 0 || F1 < k) {
+        Group<T>::sync();                                   // pickup clears are visible
+        if (F1 < k) capture_oldsky();
+        scan_free();
         ensure_noise();
         const int J = F1 < k ? k : 32 - __clz(mP);
         extract_ranks<T, NB>(grp, tid, c, mant, freem, validm, J, [&](int j, int pos) {
@@ -390,18 +445,13 @@ __device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const S
         });
     }
     // S9 dropzone respawn (env.py:205-212): same spawn_key, hence the same noise
-    if (mD != 0) {
+    if (mD != 0 || F1 - __popc(mP) < k) {
         Group<T>::sync();                                   // mask zeroing comes after the packet spawn's writes
         if (drone_warp && del_clear) sm.sg[tcell] = 0;
-    }
-    if (mD != 0 || F1 - __popc(mP) < k) {
         Group<T>::sync();
-        freem = 0; fc = 0;
-#pragma unroll
-        for (int s = 0; s < 2 * NB; ++s)
-            if (((validm >> s) & 1u) && sm.sg[slot_cell<T>(tid, s, c.H)] == 0) { freem |= 1u << s; ++fc; }
-        const int F2 = grp.sum(fc);
+        const int F2 = grp.sum(scan_free());
         if (mD != 0 || F2 < k) {
+            if (F2 < k) capture_oldsky();
             ensure_noise();
             const int J = F2 < k ? k : 32 - __clz(mD);
             extract_ranks<T, NB>(grp, tid, c, mant, freem, validm, J, [&](int j, int pos) {
@@ -417,6 +467,7 @@ __device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const S
         // p_choice[x, y] = False for survivors (row = x), [-1, -1] -> last cell; &= ~(old ground == SKY)
         if (drone_warp && surv) sm.code[x * G + y] = 1;
         Group<T>::sync();                                   // also orders the ground writes above
+        capture_oldsky();
         uint32_t candm = 0;
 #pragma unroll
         for (int s = 0; s < 2 * NB; ++s) {
