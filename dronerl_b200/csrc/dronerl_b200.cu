@@ -52,8 +52,8 @@ __device__ __forceinline__ void zero_code(const DevCfg& c, const Smem& sm, int t
 
 // ---- warp-per-env kernels (grids up to 128 cells) ---------------------------------------------
 
-template <int NB>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+template <int NB, class D>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, 4)
 k_step_warp(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint32_t* __restrict__ drones,
             const uint32_t* __restrict__ keys, const int8_t* __restrict__ actions, float* __restrict__ rewards,
             uint8_t* __restrict__ dones, float* __restrict__ obs, unsigned long long* __restrict__ stats) {
@@ -64,17 +64,18 @@ k_step_warp(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint
     float* tile = reinterpret_cast<float*>(base + c.off_tile);
     Group<32> grp{nullptr};
     zero_code(c, sm, lane, 32);
-    const int nvec = c.GS >> 4, n = c.n;
+    const D d{c};
+    const int nvec = d.GS() >> 4, n = d.n();
     const long long stride = (long long)gridDim.x * kWarpsPerBlock;
     long long e = (long long)blockIdx.x * kWarpsPerBlock + warp;
     Stats st;
     unsigned env_steps = 0;
-    const uint32_t validm = valid_slots<32, NB>(lane, c);
+    const uint32_t validm = valid_slots<32, NB>(lane, d);
 
     EnvInputs nxt = {};
     auto prefetch = [&](long long ee) {
         if (ee < c.N) {
-            if (lane < nvec) nxt.gv = reinterpret_cast<const uint4*>(ground + ee * c.GS)[lane];
+            if (lane < nvec) nxt.gv = reinterpret_cast<const uint4*>(ground + ee * d.GS())[lane];
             if (lane < n) {
                 nxt.rec = drones[ee * n + lane];
                 nxt.act = actions[ee * n + lane];
@@ -94,14 +95,14 @@ k_step_warp(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint
             reinterpret_cast<uint4*>(sm.sg)[lane] = cur.gv;
             zc = zero_bytes(cur.gv);
         }
-        const int F0 = (int)__reduce_add_sync(FULL, (unsigned)zc) - (c.GS - c.G2);   // also orders the stores above
-        env_step<32, NB>(grp, c, sm, validm, F0, cur.rec, cur.act, cur.k0, cur.k1, rewards + e * n, dones + e * n, st);
-        if (lane < nvec) reinterpret_cast<uint4*>(ground + e * c.GS)[lane] = reinterpret_cast<const uint4*>(sm.sg)[lane];
+        const int F0 = (int)__reduce_add_sync(FULL, (unsigned)zc) - (d.GS() - d.G2());   // also orders the stores above
+        env_step<32, NB>(grp, c, d, sm, validm, F0, cur.rec, cur.act, cur.k0, cur.k1, rewards + e * n, dones + e * n, st);
+        if (lane < nvec) reinterpret_cast<uint4*>(ground + e * d.GS())[lane] = reinterpret_cast<const uint4*>(sm.sg)[lane];
         if (lane < n) drones[e * n + lane] = cur.rec;
         if (obs != nullptr) {
-            obs_publish(c, sm, lane, cur.rec);
+            obs_publish(d, sm, lane, cur.rec);
             __syncwarp();
-            obs_tiles(c, sm, obs, e, tile, 0, 1, lane);
+            obs_tiles(d, sm, obs, e, tile, 0, 1, lane);
         }
         ++env_steps;
     }
@@ -127,7 +128,7 @@ k_reset_warp(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uin
         if (lane < nvec) reinterpret_cast<uint4*>(sm.sg)[lane] = make_uint4(0, 0, 0, 0);
         __syncwarp();
         uint32_t rec = 0;
-        env_reset<32, NB>(grp, c, sm, rec, kk.x, kk.y);
+        env_reset<32, NB>(grp, c, DynDims{c}, sm, rec, kk.x, kk.y);
         if (lane < nvec) reinterpret_cast<uint4*>(ground + e * c.GS)[lane] = reinterpret_cast<const uint4*>(sm.sg)[lane];
         if (lane < n) drones[e * n + lane] = rec;
         ++resets;
@@ -135,6 +136,7 @@ k_reset_warp(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uin
     if (lane == 0 && resets) atomicAdd(stats + DRL_STAT_RESETS, (unsigned long long)resets);
 }
 
+template <class D>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 k_obs_warp(const __grid_constant__ DevCfg c, const uint8_t* __restrict__ ground, const uint32_t* __restrict__ drones,
            float* __restrict__ obs) {
@@ -143,23 +145,23 @@ k_obs_warp(const __grid_constant__ DevCfg c, const uint8_t* __restrict__ ground,
     unsigned char* base = smem_raw + (size_t)warp * c.group_bytes;
     const Smem sm = carve(base, c);
     float* tile = reinterpret_cast<float*>(base + c.off_tile);
-    zero_code(c, sm, lane, 32);
-    const int nvec = c.GS >> 4, n = c.n;
+    const D d{c};
+    const int nvec = d.GS() >> 4, n = d.n();
     const long long stride = (long long)gridDim.x * kWarpsPerBlock;
     for (long long e = (long long)blockIdx.x * kWarpsPerBlock + warp; e < c.N; e += stride) {
         __syncwarp();
-        if (lane < nvec) reinterpret_cast<uint4*>(sm.sg)[lane] = reinterpret_cast<const uint4*>(ground + e * c.GS)[lane];
+        if (lane < nvec) reinterpret_cast<uint4*>(sm.sg)[lane] = reinterpret_cast<const uint4*>(ground + e * d.GS())[lane];
         const uint32_t rec = lane < n ? drones[e * n + lane] : 0u;
-        obs_publish(c, sm, lane, rec);
+        obs_publish(d, sm, lane, rec);
         __syncwarp();
-        obs_tiles(c, sm, obs, e, tile, 0, 1, lane);
+        obs_tiles(d, sm, obs, e, tile, 0, 1, lane);
     }
     tile_drain(lane);
 }
 
 // ---- CTA-per-env kernels (larger grids) -------------------------------------------------------
 
-template <int NB>
+template <int NB, class D>
 __global__ void __launch_bounds__(kCtaThreads)
 k_step_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint32_t* __restrict__ drones,
            const uint32_t* __restrict__ keys, const int8_t* __restrict__ actions, float* __restrict__ rewards,
@@ -174,7 +176,8 @@ k_step_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint3
     const int nvec = c.GS >> 4, n = c.n;
     Stats st;
     unsigned env_steps = 0;
-    const uint32_t validm = valid_slots<T, NB>(threadIdx.x, c);
+    const D d{c};
+    const uint32_t validm = valid_slots<T, NB>(threadIdx.x, d);
     __syncthreads();
     for (long long e = blockIdx.x; e < c.N; e += gridDim.x) {
         int zc = 0;
@@ -191,14 +194,14 @@ k_step_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint3
         }
         const uint2 kk = *reinterpret_cast<const uint2*>(keys + 2 * e);
         const int F0 = grp.sum(zc) - (c.GS - c.G2);     // block-wide: also publishes the ground stores
-        env_step<T, NB>(grp, c, sm, validm, F0, rec, act, kk.x, kk.y, rewards + e * n, dones + e * n, st);
+        env_step<T, NB>(grp, c, d, sm, validm, F0, rec, act, kk.x, kk.y, rewards + e * n, dones + e * n, st);
         for (int i = threadIdx.x; i < nvec; i += T)
             reinterpret_cast<uint4*>(ground + e * c.GS)[i] = reinterpret_cast<const uint4*>(sm.sg)[i];
         if (threadIdx.x < n) drones[e * n + threadIdx.x] = rec;
         if (obs != nullptr) {
-            if (warp == 0) obs_publish(c, sm, lane, rec);
+            if (warp == 0) obs_publish(d, sm, lane, rec);
             __syncthreads();
-            obs_tiles(c, sm, obs, e, tile, warp, T / 32, lane);
+            obs_tiles(d, sm, obs, e, tile, warp, T / 32, lane);
             __syncthreads();
         }
         if (threadIdx.x == 0) ++env_steps;
@@ -222,7 +225,7 @@ k_reset_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint
         for (int i = threadIdx.x; i < nvec; i += T) reinterpret_cast<uint4*>(sm.sg)[i] = make_uint4(0, 0, 0, 0);
         __syncthreads();
         uint32_t rec = 0;
-        env_reset<T, NB>(grp, c, sm, rec, kk.x, kk.y);
+        env_reset<T, NB>(grp, c, DynDims{c}, sm, rec, kk.x, kk.y);
         for (int i = threadIdx.x; i < nvec; i += T)
             reinterpret_cast<uint4*>(ground + e * c.GS)[i] = reinterpret_cast<const uint4*>(sm.sg)[i];
         if (threadIdx.x < n) drones[e * n + threadIdx.x] = rec;
@@ -232,6 +235,7 @@ k_reset_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint
     if (threadIdx.x == 0 && resets) atomicAdd(stats + DRL_STAT_RESETS, (unsigned long long)resets);
 }
 
+template <class D>
 __global__ void __launch_bounds__(kCtaThreads)
 k_obs_cta(const __grid_constant__ DevCfg c, const uint8_t* __restrict__ ground, const uint32_t* __restrict__ drones,
           float* __restrict__ obs) {
@@ -240,7 +244,7 @@ k_obs_cta(const __grid_constant__ DevCfg c, const uint8_t* __restrict__ ground, 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const Smem sm = carve(smem_raw, c);
     float* tile = reinterpret_cast<float*>(smem_raw + c.off_tile + (size_t)warp * c.tile_stride);
-    zero_code(c, sm, threadIdx.x, T);
+    const D d{c};
     const int nvec = c.GS >> 4, n = c.n;
     for (long long e = blockIdx.x; e < c.N; e += gridDim.x) {
         __syncthreads();
@@ -248,10 +252,10 @@ k_obs_cta(const __grid_constant__ DevCfg c, const uint8_t* __restrict__ ground, 
             reinterpret_cast<uint4*>(sm.sg)[i] = reinterpret_cast<const uint4*>(ground + e * c.GS)[i];
         if (warp == 0) {
             const uint32_t rec = lane < n ? drones[e * n + lane] : 0u;
-            obs_publish(c, sm, lane, rec);
+            obs_publish(d, sm, lane, rec);
         }
         __syncthreads();
-        obs_tiles(c, sm, obs, e, tile, warp, T / 32, lane);
+        obs_tiles(d, sm, obs, e, tile, warp, T / 32, lane);
     }
     tile_drain(lane);
 }
@@ -322,15 +326,40 @@ typedef void (*step_fn)(DevCfg, uint8_t*, uint32_t*, const uint32_t*, const int8
 typedef void (*reset_fn)(DevCfg, uint8_t*, uint32_t*, const uint32_t*, unsigned long long*);
 typedef void (*obs_fn)(DevCfg, const uint8_t*, const uint32_t*, float*);
 
+using D943 = Dims<9, 4, 3>;    // train_jax.py CLI defaults (train_jax.py:338-344)
+using D833 = Dims<8, 3, 3>;    // DroneEnvParams dataclass defaults (jax_impl/env/env.py:13-26)
+
+static int static_shape(const drl_env* e) {
+    const DevCfg& c = e->dc;
+    if (c.G == 9 && c.n == 4 && c.r == 3) return 1;
+    if (c.G == 8 && c.n == 3 && c.r == 3) return 2;
+    return 0;
+}
 static step_fn pick_step(const drl_env* e) {
-    if (e->warp_mode) return e->nb == 1 ? (step_fn)k_step_warp<1> : (step_fn)k_step_warp<2>;
-    return e->nb == 2 ? (step_fn)k_step_cta<2> : e->nb == 8 ? (step_fn)k_step_cta<8> : (step_fn)k_step_cta<16>;
+    if (e->warp_mode) {
+        switch (static_shape(e)) {
+            case 1: return (step_fn)k_step_warp<2, D943>;
+            case 2: return (step_fn)k_step_warp<1, D833>;
+            default: return e->nb == 1 ? (step_fn)k_step_warp<1, DynDims> : (step_fn)k_step_warp<2, DynDims>;
+        }
+    }
+    return e->nb == 2 ? (step_fn)k_step_cta<2, DynDims> : e->nb == 8 ? (step_fn)k_step_cta<8, DynDims>
+                                                                     : (step_fn)k_step_cta<16, DynDims>;
 }
 static reset_fn pick_reset(const drl_env* e) {
     if (e->warp_mode) return e->nb == 1 ? (reset_fn)k_reset_warp<1> : (reset_fn)k_reset_warp<2>;
     return e->nb == 2 ? (reset_fn)k_reset_cta<2> : e->nb == 8 ? (reset_fn)k_reset_cta<8> : (reset_fn)k_reset_cta<16>;
 }
-static obs_fn pick_obs(const drl_env* e) { return e->warp_mode ? (obs_fn)k_obs_warp : (obs_fn)k_obs_cta; }
+static obs_fn pick_obs(const drl_env* e) {
+    if (e->warp_mode) {
+        switch (static_shape(e)) {
+            case 1: return (obs_fn)k_obs_warp<D943>;
+            case 2: return (obs_fn)k_obs_warp<D833>;
+            default: return (obs_fn)k_obs_warp<DynDims>;
+        }
+    }
+    return (obs_fn)k_obs_cta<DynDims>;
+}
 
 extern "C" {
 
@@ -405,15 +434,8 @@ int drl_create(const drl_config* cfg, drl_env** out) {
 
     e->warp_mode = G2 <= 128;
     const int cell_bytes = c.W2 * 24;
-    if (e->warp_mode) {
-        e->nb = c.H <= 32 ? 1 : 2;
-        int td = n;
-        if (td * cell_bytes > 12288) { td = 8192 / cell_bytes; if (td > 1) td &= ~1; if (td < 1) td = 1; }
-        c.tile_drones = td;
-    } else {
-        e->nb = c.H <= 2 * kCtaThreads ? 2 : c.H <= 8 * kCtaThreads ? 8 : 16;
-        c.tile_drones = (n >= 2 && 2 * cell_bytes <= 12288) ? 2 : 1;
-    }
+    e->nb = e->warp_mode ? (c.H <= 32 ? 1 : 2) : (c.H <= 2 * kCtaThreads ? 2 : c.H <= 8 * kCtaThreads ? 8 : 16);
+    c.tile_drones = tile_drones_for(n, c.W2, e->warp_mode);
     c.ntiles = (n + c.tile_drones - 1) / c.tile_drones;
     c.tile_stride = round_up(c.tile_drones * cell_bytes, 128);
     c.off_code = c.GS;

@@ -53,6 +53,48 @@ struct Stats {
 
 __device__ __forceinline__ uint32_t fdiv(uint32_t x, int d, uint32_t mul) { return d == 1 ? x : __umulhi(x, mul); }
 
+// Shape policy: Dims<0,0,0> reads every dimension from DevCfg at run time; Dims<G,N,R> bakes the
+// hot shapes in so index arithmetic folds to constants and the window loops unroll.
+__host__ __device__ constexpr int tile_drones_for(int n, int W2, bool warp_mode) {
+    const int cell_bytes = W2 * 24;
+    if (warp_mode) {
+        if (n * cell_bytes <= 12288) return n;
+        int td = 8192 / cell_bytes;
+        if (td > 1) td &= ~1;
+        return td < 1 ? 1 : td;
+    }
+    return (n >= 2 && 2 * cell_bytes <= 12288) ? 2 : 1;
+}
+
+template <int G_, int N_, int R_>
+struct Dims {
+    static constexpr bool kStatic = G_ > 0;
+    static constexpr int kW = 2 * R_ + 1;
+    static constexpr int kTD = kStatic ? tile_drones_for(N_, kW * kW, G_ * G_ <= 128) : 0;
+    const DevCfg& c;
+    __device__ __forceinline__ int G() const { return kStatic ? G_ : c.G; }
+    __device__ __forceinline__ int G2() const { return kStatic ? G_ * G_ : c.G2; }
+    __device__ __forceinline__ int H() const { return kStatic ? (G_ * G_ + 1) / 2 : c.H; }
+    __device__ __forceinline__ int GS() const { return kStatic ? (G_ * G_ + 15) / 16 * 16 : c.GS; }
+    __device__ __forceinline__ int n() const { return kStatic ? N_ : c.n; }
+    __device__ __forceinline__ int r() const { return kStatic ? R_ : c.r; }
+    __device__ __forceinline__ int W() const { return kStatic ? kW : c.W; }
+    __device__ __forceinline__ int W2() const { return kStatic ? kW * kW : c.W2; }
+    __device__ __forceinline__ int center() const { return kStatic ? R_ * kW + R_ : c.center; }
+    __device__ __forceinline__ int tile_drones() const { return kStatic ? kTD : c.tile_drones; }
+    __device__ __forceinline__ int ntiles() const { return kStatic ? (N_ + (kTD ? kTD : 1) - 1) / (kTD ? kTD : 1) : c.ntiles; }
+    __device__ __forceinline__ uint32_t divG(uint32_t x) const {
+        if constexpr (kStatic) return x / (uint32_t)(G_ ? G_ : 1); else return fdiv(x, c.G, c.mulG);
+    }
+    __device__ __forceinline__ uint32_t divW(uint32_t x) const {
+        if constexpr (kStatic) return x / (uint32_t)kW; else return fdiv(x, c.W, c.mulW);
+    }
+    __device__ __forceinline__ uint32_t divN(uint32_t x) const {
+        if constexpr (kStatic) return x / (uint32_t)(N_ ? N_ : 1); else return fdiv(x, c.n, c.mulN);
+    }
+};
+using DynDims = Dims<0, 0, 0>;
+
 // ---- group primitives: warp (T == 32) or CTA of T threads ----------------------------------
 
 template <int T>
@@ -122,28 +164,28 @@ __device__ __forceinline__ Smem carve(unsigned char* base, const DevCfg& c) {
 template <int T>
 __device__ __forceinline__ int slot_cell(int tid, int s, int H) { return tid + T * (s >> 1) + (s & 1) * H; }
 
-template <int T, int NB>
-__device__ __forceinline__ uint32_t valid_slots(int tid, const DevCfg& c) {
+template <int T, int NB, class D>
+__device__ __forceinline__ uint32_t valid_slots(int tid, const D& d) {
     uint32_t m = 0;
 #pragma unroll
     for (int s = 0; s < 2 * NB; ++s) {
         const int b = tid + T * (s >> 1);
-        const int cell = b + (s & 1) * c.H;
-        if (b < c.H && cell < c.G2) m |= 1u << s;
+        const int cell = b + (s & 1) * d.H();
+        if (b < d.H() && cell < d.G2()) m |= 1u << s;
     }
     return m;
 }
 
 // mant[s] = 23-bit mantissa of jax.random.uniform(key, (G*G,))[cell(s)]  (env.py:54,78)
-template <int T, int NB>
-__device__ __forceinline__ void noise_mantissas(int tid, const DevCfg& c, uint32_t k0, uint32_t k1, uint32_t (&mant)[2 * NB]) {
+template <int T, int NB, class D>
+__device__ __forceinline__ void noise_mantissas(int tid, const D& d, uint32_t k0, uint32_t k1, uint32_t (&mant)[2 * NB]) {
 #pragma unroll
     for (int t = 0; t < NB; ++t) {
         const int b = tid + T * t;
         uint32_t o0 = 0, o1 = 0;
-        if (b < c.H) {
-            const int hi = c.H + b;
-            drl_threefry2x32(k0, k1, (uint32_t)b, hi < c.G2 ? (uint32_t)hi : 0u, o0, o1);
+        if (b < d.H()) {
+            const int hi = d.H() + b;
+            drl_threefry2x32(k0, k1, (uint32_t)b, hi < d.G2() ? (uint32_t)hi : 0u, o0, o1);
         }
         mant[2 * t] = o0 >> 9;
         mant[2 * t + 1] = o1 >> 9;
@@ -164,8 +206,8 @@ __device__ __forceinline__ void split_warp(uint32_t& k0, uint32_t& k1, uint32_t&
 // Positions of jax.lax.top_k(log(cand) + noise, k)[0 .. J_end) in rank order.  Key of a cell =
 // (cand ? mantissa + 1 : 0, G2 - cell): candidates by noise descending, ties and the -inf tail
 // (non-candidates) by ascending cell index -- XLA:CPU's total order with index tie-break.
-template <int T, int NB, class F>
-__device__ __forceinline__ void extract_ranks(Group<T>& grp, int tid, const DevCfg& c, const uint32_t (&mant)[2 * NB],
+template <int T, int NB, class D, class F>
+__device__ __forceinline__ void extract_ranks(Group<T>& grp, int tid, const D& d, const uint32_t (&mant)[2 * NB],
                                               uint32_t candm, uint32_t validm, int J_end, F&& on_pos) {
     if constexpr (T == 32) {
         // warp mode: G2 <= 128, so (mantissa + 1) << 8 | (G2 - cell) fits one 32-bit key per slot
@@ -173,7 +215,7 @@ __device__ __forceinline__ void extract_ranks(Group<T>& grp, int tid, const DevC
 #pragma unroll
         for (int s = 0; s < 2 * NB; ++s) {
             const uint32_t hi = ((candm >> s) & 1u) ? mant[s] + 1u : 0u;
-            key[s] = ((validm >> s) & 1u) ? ((hi << 8) | (uint32_t)(c.G2 - slot_cell<T>(tid, s, c.H))) : 0u;
+            key[s] = ((validm >> s) & 1u) ? ((hi << 8) | (uint32_t)(d.G2() - slot_cell<T>(tid, s, d.H()))) : 0u;
         }
         for (int j = 0; j < J_end; ++j) {
             uint32_t b = key[0];
@@ -182,7 +224,7 @@ __device__ __forceinline__ void extract_ranks(Group<T>& grp, int tid, const DevC
             const uint32_t m = __reduce_max_sync(FULL, b);
 #pragma unroll
             for (int s = 0; s < 2 * NB; ++s) key[s] = key[s] == m ? 0u : key[s];
-            on_pos(j, c.G2 - (int)(m & 0xFFu));
+            on_pos(j, d.G2() - (int)(m & 0xFFu));
         }
     } else {
         uint32_t live = validm;
@@ -193,14 +235,14 @@ __device__ __forceinline__ void extract_ranks(Group<T>& grp, int tid, const DevC
             for (int s = 0; s < 2 * NB; ++s) {
                 if ((live >> s) & 1u) {
                     const uint32_t hi = ((candm >> s) & 1u) ? mant[s] + 1u : 0u;
-                    const uint32_t lo = (uint32_t)(c.G2 - slot_cell<T>(tid, s, c.H));
+                    const uint32_t lo = (uint32_t)(d.G2() - slot_cell<T>(tid, s, d.H()));
                     if (hi > bh || (hi == bh && lo > bl)) { bh = hi; bl = lo; bs = s; }
                 }
             }
             uint32_t mh, ml;
             grp.max_pair(bh, bl, mh, ml);
             if (bs >= 0 && bh == mh && bl == ml) live &= ~(1u << bs);
-            on_pos(j, c.G2 - (int)ml);
+            on_pos(j, d.G2() - (int)ml);
         }
     }
 }
@@ -243,28 +285,29 @@ __device__ __forceinline__ void tile_store(float* gdst, const float* ssrc, int b
 // The one-hot tensor is ~90 % zeros, so the tile is zero-filled with 128-bit stores and only the
 // non-zero entries are scattered: one lane per window ROW walks its W cells (ground class -> one
 // store), then one lane per (viewer, other drone) pair marks channels 0 and 4.
-__device__ __forceinline__ void compose_tile(const DevCfg& c, const Smem& sm, int d0, int d1, float* tile, int lane) {
+template <class D>
+__device__ __forceinline__ void compose_tile(const D& d, const Smem& sm, int d0, int d1, float* tile, int lane) {
     const int nd = d1 - d0;
-    const int vecs = (nd * c.W2 * 24 + 15) >> 4;          // tile buffers are padded to 128 B
+    const int vecs = (nd * d.W2() * 24 + 15) >> 4;          // tile buffers are padded to 128 B
     float4* t4 = reinterpret_cast<float4*>(tile);
     for (int i = lane; i < vecs; i += 32) t4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     __syncwarp();
     // ground value -> channel: 0 -> none, SKY 2 -> 5, STATION 3 -> 3, DROPZONE 4 -> 2, PACKET 5 -> 1
     constexpr uint32_t kChan = (5u << 8) | (3u << 12) | (2u << 16) | (1u << 20);
-    const int rows = nd * c.W;
+    const int rows = nd * d.W();
     for (int row = lane; row < rows; row += 32) {
-        const int dd = (int)fdiv((uint32_t)row, c.W, c.mulW);
-        const int wy = row - dd * c.W;
+        const int dd = (int)d.divW((uint32_t)row);
+        const int wy = row - dd * d.W();
         const uint32_t rec = sm.sdr[d0 + dd];
-        const int gy = (int)((rec >> 8) & 0xFFu) + wy - c.r;
-        int gx = (int)(rec & 0xFFu) - c.r;
-        float* o = tile + row * c.W * 6;
-        if ((unsigned)gy >= (unsigned)c.G) {
-            for (int wx = 0; wx < c.W; ++wx) o[wx * 6 + 5] = 1.0f;          // the whole row is wall
+        const int gy = (int)((rec >> 8) & 0xFFu) + wy - d.r();
+        int gx = (int)(rec & 0xFFu) - d.r();
+        float* o = tile + row * d.W() * 6;
+        if ((unsigned)gy >= (unsigned)d.G()) {
+            for (int wx = 0; wx < d.W(); ++wx) o[wx * 6 + 5] = 1.0f;          // the whole row is wall
         } else {
-            const uint8_t* grow = sm.sg + gy * c.G;
-            for (int wx = 0; wx < c.W; ++wx, ++gx) {
-                const uint32_t g = (unsigned)gx < (unsigned)c.G ? grow[gx] : (uint32_t)SKY;
+            const uint8_t* grow = sm.sg + gy * d.G();
+            for (int wx = 0; wx < d.W(); ++wx, ++gx) {
+                const uint32_t g = (unsigned)gx < (unsigned)d.G() ? grow[gx] : (uint32_t)SKY;
                 const uint32_t ch = (kChan >> (4u * g)) & 7u;
                 if (ch) o[wx * 6 + ch] = 1.0f;
             }
@@ -272,30 +315,31 @@ __device__ __forceinline__ void compose_tile(const DevCfg& c, const Smem& sm, in
     }
     // drones: obs[d, wy, wx, 0] = 1 and [.., 4] = charge/100 where another (or the same) drone sits in
     // the window; with several drones in one cell the highest index provides the charge (bit 17 of sdr)
-    const int pairs = nd * c.n;
+    const int pairs = nd * d.n();
     for (int pi = lane; pi < pairs; pi += 32) {
-        const int dd = (int)fdiv((uint32_t)pi, c.n, c.mulN);
-        const int j = pi - dd * c.n;
+        const int dd = (int)d.divN((uint32_t)pi);
+        const int j = pi - dd * d.n();
         const uint32_t rv = sm.sdr[d0 + dd], rj = sm.sdr[j];
-        const int dx = (int)(rj & 0xFFu) - (int)(rv & 0xFFu) + c.r;
-        const int dy = (int)((rj >> 8) & 0xFFu) - (int)((rv >> 8) & 0xFFu) + c.r;
-        if (((rj >> 17) & 1u) && (unsigned)dx < (unsigned)c.W && (unsigned)dy < (unsigned)c.W) {
-            float* o = tile + ((dd * c.W2 + dy * c.W + dx) * 6);
+        const int dx = (int)(rj & 0xFFu) - (int)(rv & 0xFFu) + d.r();
+        const int dy = (int)((rj >> 8) & 0xFFu) - (int)((rv >> 8) & 0xFFu) + d.r();
+        if (((rj >> 17) & 1u) && (unsigned)dx < (unsigned)d.W() && (unsigned)dy < (unsigned)d.W()) {
+            float* o = tile + ((dd * d.W2() + dy * d.W() + dx) * 6);
             o[0] = 1.0f;
             o[4] = sm.sdf[j];
         }
     }
     // obs[:, r, r, 1] |= carrying_package
-    if (lane < nd && ((sm.sdr[d0 + lane] >> 16) & 1u)) tile[(lane * c.W2 + c.center) * 6 + 1] = 1.0f;
-    for (int d = lane + 32; d < nd; d += 32)
-        if ((sm.sdr[d0 + d] >> 16) & 1u) tile[(d * c.W2 + c.center) * 6 + 1] = 1.0f;
+    if (lane < nd && ((sm.sdr[d0 + lane] >> 16) & 1u)) tile[(lane * d.W2() + d.center()) * 6 + 1] = 1.0f;
+    for (int k = lane + 32; k < nd; k += 32)
+        if ((sm.sdr[d0 + k] >> 16) & 1u) tile[(k * d.W2() + d.center()) * 6 + 1] = 1.0f;
 }
 
 // Publish final drone records for obs: sdr[i] = record | (owns-its-cell << 17), sdf[i] = charge/100.
 // "Owns" = highest drone index in that cell: the padded_charge scatter of env.py:282-283 is applied
 // in drone order on XLA:CPU, so the last drone's charge is the one that shows.
-__device__ __forceinline__ void obs_publish(const DevCfg& c, const Smem& sm, int lane, uint32_t rec) {
-    const bool isd = lane < c.n;
+template <class D>
+__device__ __forceinline__ void obs_publish(const D& d, const Smem& sm, int lane, uint32_t rec) {
+    const bool isd = lane < d.n();
     const uint32_t grp = __match_any_sync(FULL, isd ? (rec & 0xFFFFu) : (0x80000000u | (uint32_t)lane));
     if (isd) {
         const bool owner = (31 - __clz(grp)) == lane;
@@ -305,15 +349,16 @@ __device__ __forceinline__ void obs_publish(const DevCfg& c, const Smem& sm, int
 }
 
 // Warp-level: compose + store every tile t = first, first + step, ... of env ``e``.
-__device__ __forceinline__ void obs_tiles(const DevCfg& c, const Smem& sm, float* obs, long long e, float* tile,
+template <class D>
+__device__ __forceinline__ void obs_tiles(const D& d, const Smem& sm, float* obs, long long e, float* tile,
                                           int first, int step, int lane) {
-    for (int t = first; t < c.ntiles; t += step) {
-        const int d0 = t * c.tile_drones;
-        const int d1 = min(c.n, d0 + c.tile_drones);
+    for (int t = first; t < d.ntiles(); t += step) {
+        const int d0 = t * d.tile_drones();
+        const int d1 = min(d.n(), d0 + d.tile_drones());
         tile_wait_reusable(lane);
-        compose_tile(c, sm, d0, d1, tile, lane);
-        float* gdst = obs + ((size_t)e * c.n + d0) * (size_t)(c.W2 * 6);
-        tile_store(gdst, tile, (d1 - d0) * c.W2 * 24, lane);
+        compose_tile(d, sm, d0, d1, tile, lane);
+        float* gdst = obs + ((size_t)e * d.n() + d0) * (size_t)(d.W2() * 6);
+        tile_store(gdst, tile, (d1 - d0) * d.W2() * 24, lane);
     }
 }
 
@@ -323,15 +368,15 @@ __device__ __forceinline__ void obs_tiles(const DevCfg& c, const Smem& sm, float
 // ``validm`` = valid_slots() of this thread, ``F0`` = number of free (zero) cells of that ground.
 // Drone i lives in lane i of warp 0 of the group (``rec``/``act`` valid there).
 // Postconditions: sm.sg holds the new ground, ``rec`` the new drone record, rewards/dones written.
-template <int T, int NB>
-__device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const Smem& sm, uint32_t validm, int F0,
+template <int T, int NB, class D>
+__device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const D& d, const Smem& sm, uint32_t validm, int F0,
                                          uint32_t& rec, int act, uint32_t k0, uint32_t k1, float* rewards_e,
                                          uint8_t* dones_e, Stats& st) {
     constexpr bool kWarp = Group<T>::kWarp;
     const int tid = Group<T>::tid();
     const int lane = threadIdx.x & 31;
     const bool drone_warp = kWarp || threadIdx.x < 32;
-    const int G = c.G, G2 = c.G2, n = c.n;
+    const int G = d.G(), G2 = d.G2(), n = d.n();
 
     // Which owned cells held a skyscraper BEFORE the step (spawn_air's exclude mask).  Skyscrapers only
     // ever change when a spawn runs out of free cells (the erasing-zeros edge), so the mask is captured
@@ -342,7 +387,7 @@ __device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const S
         if (!have_oldsky) {
 #pragma unroll
             for (int s = 0; s < 2 * NB; ++s)
-                if (((validm >> s) & 1u) && sm.sg[slot_cell<T>(tid, s, c.H)] == SKY) oldsky |= 1u << s;
+                if (((validm >> s) & 1u) && sm.sg[slot_cell<T>(tid, s, d.H())] == SKY) oldsky |= 1u << s;
             have_oldsky = true;
         }
     };
@@ -422,7 +467,7 @@ __device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const S
         freem = 0;
 #pragma unroll
         for (int s = 0; s < 2 * NB; ++s)
-            if (((validm >> s) & 1u) && sm.sg[slot_cell<T>(tid, s, c.H)] == 0) { freem |= 1u << s; ++fc; }
+            if (((validm >> s) & 1u) && sm.sg[slot_cell<T>(tid, s, d.H())] == 0) { freem |= 1u << s; ++fc; }
         return fc;
     };
 
@@ -431,7 +476,7 @@ __device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const S
     uint32_t mant[2 * NB];
     auto ensure_noise = [&]() {
         if (!have_split) { split_warp(k0, k1, sk0, sk1); have_split = true; }   // key, spawn_key = split(key)
-        if (!have_noise) { noise_mantissas<T, NB>(tid, c, sk0, sk1, mant); have_noise = true; }
+        if (!have_noise) { noise_mantissas<T, NB>(tid, d, sk0, sk1, mant); have_noise = true; }
     };
 
     if (mP != 0 || F1 < k) {
@@ -440,7 +485,7 @@ __device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const S
         scan_free();
         ensure_noise();
         const int J = F1 < k ? k : 32 - __clz(mP);
-        extract_ranks<T, NB>(grp, tid, c, mant, freem, validm, J, [&](int j, int pos) {
+        extract_ranks<T, NB>(grp, tid, d, mant, freem, validm, J, [&](int j, int pos) {
             if (tid == 0) sm.sg[pos] = (j < n && ((mP >> j) & 1u)) ? PACKET : 0;
         });
     }
@@ -454,7 +499,7 @@ __device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const S
             if (F2 < k) capture_oldsky();
             ensure_noise();
             const int J = F2 < k ? k : 32 - __clz(mD);
-            extract_ranks<T, NB>(grp, tid, c, mant, freem, validm, J, [&](int j, int pos) {
+            extract_ranks<T, NB>(grp, tid, d, mant, freem, validm, J, [&](int j, int pos) {
                 if (tid == 0) sm.sg[pos] = (j < n && ((mD >> j) & 1u)) ? DROPZONE : 0;
             });
         }
@@ -471,13 +516,13 @@ __device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const S
         uint32_t candm = 0;
 #pragma unroll
         for (int s = 0; s < 2 * NB; ++s) {
-            const int cell = slot_cell<T>(tid, s, c.H);
+            const int cell = slot_cell<T>(tid, s, d.H());
             if (((validm >> s) & 1u) && !((oldsky >> s) & 1u) && cell != G2 - 1 && sm.code[cell] == 0) candm |= 1u << s;
         }
-        noise_mantissas<T, NB>(tid, c, sk0, sk1, mant);
-        extract_ranks<T, NB>(grp, tid, c, mant, candm, validm, 32 - __clz(mDone), [&](int j, int pos) {
+        noise_mantissas<T, NB>(tid, d, sk0, sk1, mant);
+        extract_ranks<T, NB>(grp, tid, d, mant, candm, validm, 32 - __clz(mDone), [&](int j, int pos) {
             if (drone_warp && lane == j && done) {
-                x = (int)fdiv((uint32_t)pos, G, c.mulG);    // rank i -> drone i: x = pos // G, y = pos % G
+                x = (int)d.divG((uint32_t)pos);    // rank i -> drone i: x = pos // G, y = pos % G
                 y = pos - x * G;
                 if (sm.sg[pos] == PACKET) {                 // package_mask[new_x, new_y]: flat index x*G+y == pos
                     carry = 1;
@@ -494,15 +539,15 @@ __device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const S
 }
 
 // ---- one env reset (env.py:89-135) -------------------------------------------------------------
-template <int T, int NB>
-__device__ __forceinline__ void env_reset(Group<T>& grp, const DevCfg& c, const Smem& sm, uint32_t& rec, uint32_t k0,
+template <int T, int NB, class D>
+__device__ __forceinline__ void env_reset(Group<T>& grp, const DevCfg& c, const D& d, const Smem& sm, uint32_t& rec, uint32_t k0,
                                           uint32_t k1) {
     constexpr bool kWarp = Group<T>::kWarp;
     const int tid = Group<T>::tid();
     const int lane = threadIdx.x & 31;
     const bool drone_warp = kWarp || threadIdx.x < 32;
-    const int G = c.G, G2 = c.G2, n = c.n;
-    const uint32_t validm = valid_slots<T, NB>(tid, c);
+    const int G = d.G(), G2 = d.G2(), n = d.n();
+    const uint32_t validm = valid_slots<T, NB>(tid, d);
     uint32_t mant[2 * NB];
     uint32_t sk0, sk1;
     const int objs[4] = {PACKET, DROPZONE, STATION, SKY};
@@ -513,10 +558,10 @@ __device__ __forceinline__ void env_reset(Group<T>& grp, const DevCfg& c, const 
         uint32_t freem = 0;
 #pragma unroll
         for (int s = 0; s < 2 * NB; ++s)
-            if (((validm >> s) & 1u) && sm.sg[slot_cell<T>(tid, s, c.H)] == 0) freem |= 1u << s;
-        noise_mantissas<T, NB>(tid, c, sk0, sk1, mant);
+            if (((validm >> s) & 1u) && sm.sg[slot_cell<T>(tid, s, d.H())] == 0) freem |= 1u << s;
+        noise_mantissas<T, NB>(tid, d, sk0, sk1, mant);
         const int obj = objs[t];
-        extract_ranks<T, NB>(grp, tid, c, mant, freem, validm, c.k_reset[t], [&](int, int pos) {
+        extract_ranks<T, NB>(grp, tid, d, mant, freem, validm, c.k_reset[t], [&](int, int pos) {
             if (tid == 0) sm.sg[pos] = (uint8_t)obj;
         });
         Group<T>::sync();
@@ -526,14 +571,14 @@ __device__ __forceinline__ void env_reset(Group<T>& grp, const DevCfg& c, const 
     uint32_t candm = 0;
 #pragma unroll
     for (int s = 0; s < 2 * NB; ++s) {
-        const int cell = slot_cell<T>(tid, s, c.H);
+        const int cell = slot_cell<T>(tid, s, d.H());
         if (((validm >> s) & 1u) && cell != G2 - 1 && sm.sg[cell] != SKY) candm |= 1u << s;
     }
-    noise_mantissas<T, NB>(tid, c, sk0, sk1, mant);
+    noise_mantissas<T, NB>(tid, d, sk0, sk1, mant);
     int x = 0, y = 0;
-    extract_ranks<T, NB>(grp, tid, c, mant, candm, validm, n, [&](int j, int pos) {
+    extract_ranks<T, NB>(grp, tid, d, mant, candm, validm, n, [&](int j, int pos) {
         if (drone_warp && lane == j) {
-            x = (int)fdiv((uint32_t)pos, G, c.mulG);
+            x = (int)d.divG((uint32_t)pos);
             y = pos - x * G;
         }
     });
