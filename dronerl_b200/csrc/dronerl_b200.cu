@@ -10,18 +10,13 @@
 
 #include "../../include/dronerl_b200.h"
 #include "env_kernels.cuh"
+#include "step_warp.cuh"
 
 using namespace drl;
 
 // =================================================================================================
 // kernels
 // =================================================================================================
-
-struct EnvInputs {   // per-env inputs, prefetched one env ahead in warp mode
-    uint4 gv;
-    uint32_t rec, k0, k1;
-    int act;
-};
 
 __device__ __forceinline__ void flush_stats(const Stats& st, unsigned env_steps, unsigned long long* stats, int lane) {
     const unsigned d = __reduce_add_sync(FULL, st.dones), c = __reduce_add_sync(FULL, st.crashes),
@@ -38,12 +33,6 @@ __device__ __forceinline__ void flush_stats(const Stats& st, unsigned env_steps,
     }
 }
 
-// number of zero bytes in 16 bytes of ground (free cells; row padding is zero too)
-__device__ __forceinline__ int zero_bytes(const uint4& v) {
-    return (__popc(__vcmpeq4(v.x, 0u)) + __popc(__vcmpeq4(v.y, 0u)) + __popc(__vcmpeq4(v.z, 0u)) +
-            __popc(__vcmpeq4(v.w, 0u))) >> 3;
-}
-
 __device__ __forceinline__ void zero_code(const DevCfg& c, const Smem& sm, int tid, int nthreads) {
     uint32_t* w = reinterpret_cast<uint32_t*>(sm.code);
     const int words = (c.off_sdr - c.off_code) >> 2;
@@ -52,62 +41,17 @@ __device__ __forceinline__ void zero_code(const DevCfg& c, const Smem& sm, int t
 
 // ---- warp-per-env kernels (grids up to 128 cells) ---------------------------------------------
 
-template <int NB, class D>
+template <int NB, int Q, class D>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32, 4)
 k_step_warp(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint32_t* __restrict__ drones,
             const uint32_t* __restrict__ keys, const int8_t* __restrict__ actions, float* __restrict__ rewards,
             uint8_t* __restrict__ dones, float* __restrict__ obs, unsigned long long* __restrict__ stats) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    unsigned char* base = smem_raw + (size_t)warp * c.group_bytes;
-    const Smem sm = carve(base, c);
-    float* tile = reinterpret_cast<float*>(base + c.off_tile);
-    Group<32> grp{nullptr};
-    zero_code(c, sm, lane, 32);
+    const int warp = threadIdx.x >> 5;
     const D d{c};
-    const int nvec = d.GS() >> 4, n = d.n();
-    const long long stride = (long long)gridDim.x * kWarpsPerBlock;
-    long long e = (long long)blockIdx.x * kWarpsPerBlock + warp;
-    Stats st;
-    unsigned env_steps = 0;
-    const uint32_t validm = valid_slots<32, NB>(lane, d);
-
-    EnvInputs nxt = {};
-    auto prefetch = [&](long long ee) {
-        if (ee < c.N) {
-            if (lane < nvec) nxt.gv = reinterpret_cast<const uint4*>(ground + ee * d.GS())[lane];
-            if (lane < n) {
-                nxt.rec = drones[ee * n + lane];
-                nxt.act = actions[ee * n + lane];
-            }
-            const uint2 kk = *reinterpret_cast<const uint2*>(keys + 2 * ee);
-            nxt.k0 = kk.x;
-            nxt.k1 = kk.y;
-        }
-    };
-    prefetch(e);
-    for (; e < c.N; e += stride) {
-        EnvInputs cur = nxt;
-        prefetch(e + stride);
-        __syncwarp();
-        int zc = 0;
-        if (lane < nvec) {
-            reinterpret_cast<uint4*>(sm.sg)[lane] = cur.gv;
-            zc = zero_bytes(cur.gv);
-        }
-        const int F0 = (int)__reduce_add_sync(FULL, (unsigned)zc) - (d.GS() - d.G2());   // also orders the stores above
-        env_step<32, NB>(grp, c, d, sm, validm, F0, cur.rec, cur.act, cur.k0, cur.k1, rewards + e * n, dones + e * n, st);
-        if (lane < nvec) reinterpret_cast<uint4*>(ground + e * d.GS())[lane] = reinterpret_cast<const uint4*>(sm.sg)[lane];
-        if (lane < n) drones[e * n + lane] = cur.rec;
-        if (obs != nullptr) {
-            obs_publish(d, sm, lane, cur.rec);
-            __syncwarp();
-            obs_tiles(d, sm, obs, e, tile, 0, 1, lane);
-        }
-        ++env_steps;
-    }
-    tile_drain(lane);
-    flush_stats(st, env_steps, stats, lane);
+    step_warp_body<NB, Q, D>(c, d, smem_raw + (size_t)warp * c.group_bytes, ground, drones, keys, actions, rewards, dones,
+                             obs, stats, (long long)blockIdx.x * kWarpsPerBlock + warp,
+                             (long long)gridDim.x * kWarpsPerBlock);
 }
 
 template <int NB>
@@ -184,7 +128,7 @@ k_step_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint3
         for (int i = threadIdx.x; i < nvec; i += T) {
             const uint4 v = reinterpret_cast<const uint4*>(ground + e * c.GS)[i];
             reinterpret_cast<uint4*>(sm.sg)[i] = v;
-            zc += zero_bytes(v);
+            zc += zero_bytes16(v);
         }
         uint32_t rec = 0;
         int act = 4;
@@ -290,6 +234,7 @@ struct drl_env {
     DevCfg dc;
     bool warp_mode;
     int nb;               // threefry blocks per thread (template instance)
+    int envs_per_warp;    // warp mode: envs one warp steps together (4, 2 or 1)
     int smem_bytes;       // dynamic shared memory per CTA
     int grid_step, grid_reset, grid_obs;
     int sm_count;
@@ -335,12 +280,16 @@ static int static_shape(const drl_env* e) {
     if (c.G == 8 && c.n == 3 && c.r == 3) return 2;
     return 0;
 }
+template <int NB, class D>
+static step_fn step_warp_q(int q) {
+    return q == 4 ? (step_fn)k_step_warp<NB, 4, D> : q == 2 ? (step_fn)k_step_warp<NB, 2, D> : (step_fn)k_step_warp<NB, 1, D>;
+}
 static step_fn pick_step(const drl_env* e) {
     if (e->warp_mode) {
         switch (static_shape(e)) {
-            case 1: return (step_fn)k_step_warp<2, D943>;
-            case 2: return (step_fn)k_step_warp<1, D833>;
-            default: return e->nb == 1 ? (step_fn)k_step_warp<1, DynDims> : (step_fn)k_step_warp<2, DynDims>;
+            case 1: return (step_fn)k_step_warp<2, 4, D943>;
+            case 2: return (step_fn)k_step_warp<1, 4, D833>;
+            default: return e->nb == 1 ? step_warp_q<1, DynDims>(e->envs_per_warp) : step_warp_q<2, DynDims>(e->envs_per_warp);
         }
     }
     return e->nb == 2 ? (step_fn)k_step_cta<2, DynDims> : e->nb == 8 ? (step_fn)k_step_cta<8, DynDims>
@@ -438,8 +387,10 @@ int drl_create(const drl_config* cfg, drl_env** out) {
     c.tile_drones = tile_drones_for(n, c.W2, e->warp_mode);
     c.ntiles = (n + c.tile_drones - 1) / c.tile_drones;
     c.tile_stride = round_up(c.tile_drones * cell_bytes, 128);
-    c.off_code = c.GS;
-    c.off_sdr = c.off_code + round_up((int)G2, 16);
+    e->envs_per_warp = !e->warp_mode ? 1 : n <= 8 ? 4 : n <= 16 ? 2 : 1;
+    const int Q = e->envs_per_warp;
+    c.off_code = Q * c.GS;
+    c.off_sdr = c.off_code + Q * round_up((int)G2, 16);
     c.off_sdf = c.off_sdr + 128;
     c.off_misc = c.off_sdf + 128;
     c.off_red = c.off_misc + 16;
@@ -461,8 +412,9 @@ int drl_create(const drl_config* cfg, drl_env** out) {
     const int threads = e->warp_mode ? kWarpsPerBlock * 32 : kCtaThreads;
     const void* fns[3] = {(const void*)pick_step(e), (const void*)pick_reset(e), (const void*)pick_obs(e)};
     int* grids[3] = {&e->grid_step, &e->grid_reset, &e->grid_obs};
-    const long long units = e->warp_mode ? (c.N + kWarpsPerBlock - 1) / kWarpsPerBlock : c.N;
     for (int i = 0; i < 3; ++i) {
+        const long long per_cta = e->warp_mode ? (long long)kWarpsPerBlock * (i == 0 ? Q : 1) : 1;
+        const long long units = (c.N + per_cta - 1) / per_cta;
         cudaError_t ce = cudaFuncSetAttribute(fns[i], cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem_bytes);
         int per_sm = 0;
         if (ce == cudaSuccess) ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fns[i], threads, e->smem_bytes);

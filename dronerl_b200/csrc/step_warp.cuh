@@ -1,0 +1,321 @@
+// Warp-mode fused step + get_obs kernel (grids up to 128 cells): one warp steps Q consecutive envs.
+//
+// The per-drone part of a step (move, collisions, charge, pickup/delivery, rewards) needs only
+// n lanes, and the two key splits only 2, so a warp runs them for Q = 4 (n <= 8), 2 (n <= 16) or 1
+// envs at once: env q of the group owns lanes [q*S, (q+1)*S), S = 32/Q; match_any keys and ballots
+// are segmented by q.  What needs the whole warp -- threefry noise over the grid, rank extraction,
+// observation tiles -- then runs env by env, and only for the envs that need it.
+// Semantics: /root/reference/jax_impl/env/env.py:137-250 (step) and :274-309 (get_obs).
+#pragma once
+#include "env_kernels.cuh"
+
+namespace drl {
+
+struct GroupInputs {   // inputs of one group of Q envs, prefetched one group ahead
+    uint4 gv;
+    uint32_t rec, k0, k1;
+    int act;
+};
+
+// number of zero bytes in 16 bytes of ground (free cells; row padding is zero too)
+__device__ __forceinline__ int zero_bytes16(const uint4& v) {
+    // ground values are < 8: a byte is non-zero iff one of its low three bits is set
+    auto nz = [](uint32_t w) { return __popc((w | (w >> 1) | (w >> 2)) & 0x01010101u); };
+    return 16 - (nz(v.x) + nz(v.y) + nz(v.z) + nz(v.w));
+}
+
+template <int NB, int Q, class D>
+__device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsigned char* base, uint8_t* __restrict__ ground,
+                                               uint32_t* __restrict__ drones, const uint32_t* __restrict__ keys,
+                                               const int8_t* __restrict__ actions, float* __restrict__ rewards,
+                                               uint8_t* __restrict__ dones, float* __restrict__ obs,
+                                               unsigned long long* __restrict__ stats, long long first_group,
+                                               long long group_stride) {
+    constexpr int S = 32 / Q;
+    constexpr uint32_t SM = Q == 1 ? FULL : ((1u << S) - 1u);
+    const int lane = threadIdx.x & 31;
+    const int sub = lane / S, li = lane % S;
+    const int G = d.G(), G2 = d.G2(), GS = d.GS(), n = d.n();
+    const int CP = (G2 + 15) & ~15;
+    uint8_t* const sg_all = base;
+    uint8_t* const code_all = base + c.off_code;
+    uint32_t* const sdr = reinterpret_cast<uint32_t*>(base + c.off_sdr);
+    float* const sdf = reinterpret_cast<float*>(base + c.off_sdf);
+    int* const zcs = reinterpret_cast<int*>(base + c.off_misc);
+    float* const tile = reinterpret_cast<float*>(base + c.off_tile);
+    uint8_t* const sg = sg_all + sub * GS;       // this lane's env
+    Group<32> grp{nullptr};
+    {   // survivor-mark scratch starts (and is always restored to) all zero
+        uint32_t* w = reinterpret_cast<uint32_t*>(code_all);
+        for (int i = lane; i < (Q * CP) >> 2; i += 32) w[i] = 0u;
+    }
+    const int nvec = GS >> 4;                     // 16-byte vectors per ground row; Q * nvec <= 32
+    const uint32_t validm = valid_slots<32, NB>(lane, d);
+    const int k = c.k_spawn;
+    Stats st;
+    unsigned env_steps = 0;
+
+    GroupInputs nxt = {};
+    auto prefetch = [&](long long g) {
+        const long long e0 = g * Q;
+        if (e0 < c.N) {
+            const int nq = (int)min((long long)Q, c.N - e0);
+            if (lane < nvec * nq) nxt.gv = reinterpret_cast<const uint4*>(ground + e0 * GS)[lane];
+            if (sub < nq) {
+                if (li < n) {
+                    nxt.rec = drones[(e0 + sub) * n + li];
+                    nxt.act = actions[(e0 + sub) * n + li];
+                }
+                const uint2 kk = *reinterpret_cast<const uint2*>(keys + 2 * (e0 + sub));
+                nxt.k0 = kk.x;
+                nxt.k1 = kk.y;
+            }
+        }
+    };
+    long long g = first_group;
+    prefetch(g);
+    for (; g * Q < c.N; g += group_stride) {
+        const long long e0 = g * Q;
+        const int nq = (int)min((long long)Q, c.N - e0);
+        const GroupInputs cur = nxt;
+        prefetch(g + group_stride);
+        const bool act_env = sub < nq;
+        const bool isd = act_env && li < n;
+        const long long e = e0 + sub;
+
+        // ---- stage the ground rows of the group, count free cells per env ---------------------------
+        __syncwarp();
+        {
+            int zc = 0;
+            if (lane < nvec * nq) {
+                reinterpret_cast<uint4*>(sg_all)[lane] = cur.gv;
+                zc = zero_bytes16(cur.gv);
+            }
+            if constexpr (Q == 1) {
+                zc = (int)__reduce_add_sync(FULL, (unsigned)zc);
+                if (lane == 0) zcs[0] = zc;
+            } else {
+                // segmented sum over the nvec lanes of each env
+#pragma unroll
+                for (int q = 0; q < Q; ++q) {
+                    const uint32_t m = ((1u << nvec) - 1u) << (q * nvec);
+                    if ((m >> lane) & 1u) {
+                        const int r = (int)__reduce_add_sync(m, (unsigned)zc);
+                        if (lane == q * nvec) zcs[q] = r;
+                    }
+                }
+            }
+        }
+        __syncwarp();
+        const int F0 = zcs[sub] - (GS - G2);
+
+        // ---- per-drone phase, all envs of the group at once (env.py:145-194, 215-219) -----------------
+        int x = cur.rec & 0xFFu, y = (cur.rec >> 8) & 0xFFu;
+        const bool carry_old = (cur.rec >> 16) & 1u;
+        int ch = cur.rec >> 24;
+        const int act = cur.act;
+        const int nx = x + (act == A_RIGHT) - (act == A_LEFT);
+        const int ny = y + (act == A_DOWN) - (act == A_UP);
+        const bool off = (unsigned)nx >= (unsigned)G || (unsigned)ny >= (unsigned)G;
+        const int cell = (isd && !off) ? sg[ny * G + nx] : 0;
+        const bool sky = cell == SKY;
+        // identical targets collide; keys carry the env slot so groups never mix envs
+        const uint32_t uniq = 0x80000000u | (uint32_t)lane;
+        const uint32_t pk = (isd && !off) ? ((uint32_t)sub << 16 | (uint32_t)(ny * G + nx)) : uniq;
+        const bool coll = __popc(__match_any_sync(FULL, pk)) > 1;
+        const bool collided = off | sky | coll;
+        const bool charging = (cell == STATION) && !collided;
+        const bool discharging = !charging && !collided;
+        int cc = ch;
+        cc = min(max(cc + (charging ? c.charge : 0), 0), 100);
+        cc = min(max(cc - (discharging ? c.discharge : 0), 0), 100);
+        const bool done = isd && (collided || cc == 0);
+        const bool surv = isd && !done;
+        ch = done ? 100 : cc;
+        const bool picked = (cell == PACKET) && surv && !carry_old;
+        const bool delivered = (cell == DROPZONE) && surv && carry_old;
+        int carry = ((carry_old && surv) || picked) && !delivered;
+        // mask.at[new_y, new_x].set(v): -1 wraps to G-1, >= G dropped, last update per cell wins
+        const int ty = ny < 0 ? G - 1 : ny, tx = nx < 0 ? G - 1 : nx;
+        const bool tvalid = isd && ty < G && tx < G;
+        const int tcell = ty * G + tx;
+        const uint32_t tg = __match_any_sync(FULL, tvalid ? ((uint32_t)sub << 16 | (uint32_t)tcell) : uniq);
+        const bool last = (31 - __clz(tg)) == lane;
+        const bool pick_clear = tvalid && last && picked;
+        const bool del_clear = tvalid && last && delivered;
+        const int sh = sub * S;
+        const uint32_t mP = (__ballot_sync(FULL, isd && (delivered || (done && carry_old))) >> sh) & SM;
+        const uint32_t mD = (__ballot_sync(FULL, delivered) >> sh) & SM;
+        const uint32_t mDone = (__ballot_sync(FULL, done) >> sh) & SM;
+        const int npick = __popc((__ballot_sync(FULL, pick_clear) >> sh) & SM);
+        if (pick_clear) sg[tcell] = 0;
+        x = nx; y = ny;
+        if (isd) {
+            float rw = 0.0f;   // fp32, the reference's order, no contraction
+            rw = __fadd_rn(rw, __fmul_rn(c.rw_crash, done ? 1.0f : 0.0f));
+            rw = __fadd_rn(rw, __fmul_rn(c.rw_pickup, picked ? 1.0f : 0.0f));
+            rw = __fadd_rn(rw, __fmul_rn(c.rw_delivery, delivered ? 1.0f : 0.0f));
+            rw = __fadd_rn(rw, __fmul_rn(c.rw_charge, charging ? 1.0f : 0.0f));
+            rewards[e * n + li] = rw;
+            dones[e * n + li] = done ? 1 : 0;
+            st.dones += done; st.crashes += collided; st.pickups += picked; st.deliveries += delivered;
+            st.charging += charging;
+        }
+        const int F1 = F0 + npick;
+        const bool need_p = act_env && (mP != 0 || F1 < k);
+        const bool need_d = act_env && (mD != 0 || F1 - __popc(mP) < k);
+        const bool need_r = act_env && mDone != 0;
+        const uint32_t needs = __ballot_sync(FULL, li == 0 && (need_p || need_d || need_r));
+
+        // ---- key splits of every env of the group in one pass each (env.py:197, 224) --------------------
+        uint32_t sk0 = 0, sk1 = 0, rk0 = 0, rk1 = 0;   // spawn_key (ground spawns), spawn_key of spawn_air
+        if (needs != 0) {
+            uint32_t a, b;
+            drl_threefry2x32(cur.k0, cur.k1, (uint32_t)(li & 1), (uint32_t)(li & 1) + 2u, a, b);
+            const uint32_t n0 = __shfl_sync(FULL, a, sh), n1 = __shfl_sync(FULL, a, sh + 1);
+            sk0 = __shfl_sync(FULL, b, sh);
+            sk1 = __shfl_sync(FULL, b, sh + 1);
+            if (__any_sync(FULL, need_r)) {
+                drl_threefry2x32(n0, n1, (uint32_t)(li & 1), (uint32_t)(li & 1) + 2u, a, b);
+                rk0 = __shfl_sync(FULL, b, sh);
+                rk1 = __shfl_sync(FULL, b, sh + 1);
+            }
+        }
+
+        // ---- whole-warp work, env by env, only where something spawns ---------------------------------
+        int rx = x, ry = y;                       // positions after respawn
+        for (uint32_t todo = needs; todo != 0; todo &= todo - 1) {
+            const int q = (__ffs(todo) - 1) / S;
+            const int ql = q * S;                 // lane of drone 0 of env q
+            uint8_t* const sgq = sg_all + q * GS;
+            uint8_t* const codeq = code_all + q * CP;
+            const uint32_t qP = __shfl_sync(FULL, mP, ql), qD = __shfl_sync(FULL, mD, ql);
+            const uint32_t qDone = __shfl_sync(FULL, mDone, ql);
+            const int qF1 = __shfl_sync(FULL, F1, ql);
+            const uint32_t qs0 = __shfl_sync(FULL, sk0, ql), qs1 = __shfl_sync(FULL, sk1, ql);
+            const bool mine = sub == q;
+
+            // skyscrapers of the OLD ground (spawn_air's exclude): they only change in the erasing-zeros
+            // edge, so capture lazily -- right before such an edge, or at respawn time
+            uint32_t oldsky = 0;
+            bool have_oldsky = false;
+            auto capture_oldsky = [&]() {
+                if (!have_oldsky) {
+#pragma unroll
+                    for (int s = 0; s < 2 * NB; ++s)
+                        if (((validm >> s) & 1u) && sgq[slot_cell<32>(lane, s, d.H())] == SKY) oldsky |= 1u << s;
+                    have_oldsky = true;
+                }
+            };
+            uint32_t freem = 0;
+            auto scan_free = [&]() {
+                int fc = 0;
+                freem = 0;
+#pragma unroll
+                for (int s = 0; s < 2 * NB; ++s)
+                    if (((validm >> s) & 1u) && sgq[slot_cell<32>(lane, s, d.H())] == 0) { freem |= 1u << s; ++fc; }
+                return fc;
+            };
+            uint32_t mant[2 * NB];
+            bool have_noise = false;
+            auto ensure_noise = [&]() {
+                if (!have_noise) { noise_mantissas<32, NB>(lane, d, qs0, qs1, mant); have_noise = true; }
+            };
+
+            // S8 packet respawn (env.py:197-203)
+            if (qP != 0 || qF1 < k) {
+                __syncwarp();                                       // pickup clears are visible
+                if (qF1 < k) capture_oldsky();
+                scan_free();
+                ensure_noise();
+                const int J = qF1 < k ? k : 32 - __clz(qP);
+                extract_ranks<32, NB>(grp, lane, d, mant, freem, validm, J, [&](int j, int pos) {
+                    if (lane == 0) sgq[pos] = (j < n && ((qP >> j) & 1u)) ? PACKET : 0;
+                });
+            }
+            // S9 dropzone respawn (env.py:205-212): same spawn_key, hence the same noise
+            if (qD != 0 || qF1 - __popc(qP) < k) {
+                __syncwarp();                                       // mask zeroing follows the packet spawn's writes
+                if (mine && del_clear) sgq[tcell] = 0;
+                __syncwarp();
+                const int F2 = (int)__reduce_add_sync(FULL, (unsigned)scan_free());
+                if (qD != 0 || F2 < k) {
+                    if (F2 < k) capture_oldsky();
+                    ensure_noise();
+                    const int J = F2 < k ? k : 32 - __clz(qD);
+                    extract_ranks<32, NB>(grp, lane, d, mant, freem, validm, J, [&](int j, int pos) {
+                        if (lane == 0) sgq[pos] = (j < n && ((qD >> j) & 1u)) ? DROPZONE : 0;
+                    });
+                }
+            }
+            // S11 respawn (env.py:222-230) and S12 pickup on respawn (env.py:233-241)
+            if (qDone != 0) {
+                const uint32_t qr0 = __shfl_sync(FULL, rk0, ql), qr1 = __shfl_sync(FULL, rk1, ql);
+                // p_choice[x, y] = False for survivors (row = x), [-1, -1] -> last cell; &= ~(old ground == SKY)
+                if (mine && surv) codeq[x * G + y] = 1;
+                __syncwarp();                                       // also orders the ground writes above
+                capture_oldsky();
+                uint32_t candm = 0;
+#pragma unroll
+                for (int s = 0; s < 2 * NB; ++s) {
+                    const int cl = slot_cell<32>(lane, s, d.H());
+                    if (((validm >> s) & 1u) && !((oldsky >> s) & 1u) && cl != G2 - 1 && codeq[cl] == 0) candm |= 1u << s;
+                }
+                noise_mantissas<32, NB>(lane, d, qr0, qr1, mant);
+                extract_ranks<32, NB>(grp, lane, d, mant, candm, validm, 32 - __clz(qDone), [&](int j, int pos) {
+                    if (lane == ql + j && done) {
+                        rx = (int)d.divG((uint32_t)pos);             // rank i -> drone i: x = pos // G, y = pos % G
+                        ry = pos - rx * G;
+                        if (sgq[pos] == PACKET) {                    // package_mask[new_x, new_y]: flat x*G+y == pos
+                            carry = 1;
+                            sgq[pos] = 0;
+                            st.respawn_pickups += 1;
+                        }
+                    }
+                });
+                if (mine && surv) codeq[x * G + y] = 0;              // restore the all-zero invariant
+            }
+        }
+        __syncwarp();
+
+        // ---- write back, observations -----------------------------------------------------------------
+        const uint32_t rec = (uint32_t)rx | ((uint32_t)ry << 8) | ((uint32_t)carry << 16) | ((uint32_t)ch << 24);
+        if (lane < nvec * nq) reinterpret_cast<uint4*>(ground + e0 * GS)[lane] = reinterpret_cast<const uint4*>(sg_all)[lane];
+        if (isd) drones[e * n + li] = rec;
+        if (obs != nullptr) {
+            // sdr[lane] = record | owns-its-cell << 17 (highest drone index per cell shows its charge)
+            const uint32_t og = __match_any_sync(FULL, isd ? ((uint32_t)sub << 16 | (rec & 0xFFFFu)) : uniq);
+            if (isd) {
+                sdr[lane] = (rec & 0xFF01FFFFu) | (((31 - __clz(og)) == lane) ? (1u << 17) : 0u);
+                sdf[lane] = __fdiv_rn((float)ch, 100.0f);
+            }
+            __syncwarp();
+            for (int q = 0; q < nq; ++q) {
+                Smem smq;
+                smq.sg = sg_all + q * GS;
+                smq.code = code_all + q * CP;
+                smq.sdr = sdr + q * S;
+                smq.sdf = sdf + q * S;
+                smq.misc = nullptr;
+                obs_tiles(d, smq, obs, e0 + q, tile, 0, 1, lane);
+            }
+        }
+        env_steps += nq;
+    }
+    tile_drain(lane);
+    // episode counters: one atomic per counter per warp
+    const unsigned sd = __reduce_add_sync(FULL, st.dones), sc = __reduce_add_sync(FULL, st.crashes),
+                   sp = __reduce_add_sync(FULL, st.pickups), sv = __reduce_add_sync(FULL, st.deliveries),
+                   sg_ = __reduce_add_sync(FULL, st.charging), sr = __reduce_add_sync(FULL, st.respawn_pickups);
+    if (lane == 0) {
+        if (env_steps) atomicAdd(stats + 0, (unsigned long long)env_steps);
+        if (sd) atomicAdd(stats + 1, (unsigned long long)sd);
+        if (sc) atomicAdd(stats + 2, (unsigned long long)sc);
+        if (sp) atomicAdd(stats + 3, (unsigned long long)sp);
+        if (sv) atomicAdd(stats + 4, (unsigned long long)sv);
+        if (sg_) atomicAdd(stats + 5, (unsigned long long)sg_);
+        if (sr) atomicAdd(stats + 6, (unsigned long long)sr);
+    }
+}
+
+}  // namespace drl
