@@ -42,7 +42,7 @@ __device__ __forceinline__ void zero_code(const DevCfg& c, const Smem& sm, int t
 // ---- warp-per-env kernels (grids up to 128 cells) ---------------------------------------------
 
 template <int NB, int Q, class D>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32, 4)
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, 3)
 k_step_warp(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint32_t* __restrict__ drones,
             const uint32_t* __restrict__ keys, const int8_t* __restrict__ actions, float* __restrict__ rewards,
             uint8_t* __restrict__ dones, float* __restrict__ obs, unsigned long long* __restrict__ stats) {
@@ -89,6 +89,7 @@ k_obs_warp(const __grid_constant__ DevCfg c, const uint8_t* __restrict__ ground,
     unsigned char* base = smem_raw + (size_t)warp * c.group_bytes;
     const Smem sm = carve(base, c);
     float* tile = reinterpret_cast<float*>(base + c.off_tile);
+    int tsel = 0;
     const D d{c};
     const int nvec = d.GS() >> 4, n = d.n();
     const long long stride = (long long)gridDim.x * kWarpsPerBlock;
@@ -98,7 +99,7 @@ k_obs_warp(const __grid_constant__ DevCfg c, const uint8_t* __restrict__ ground,
         const uint32_t rec = lane < n ? drones[e * n + lane] : 0u;
         obs_publish(d, sm, lane, rec);
         __syncwarp();
-        obs_tiles(d, sm, obs, e, tile, 0, 1, lane);
+        obs_tiles(d, c, sm, obs, e, tile, tsel, 0, 1, lane);
     }
     tile_drain(lane);
 }
@@ -114,7 +115,8 @@ k_step_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint3
     constexpr int T = kCtaThreads;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const Smem sm = carve(smem_raw, c);
-    float* tile = reinterpret_cast<float*>(smem_raw + c.off_tile + (size_t)warp * c.tile_stride);
+    float* tile = reinterpret_cast<float*>(smem_raw + c.off_tile + (size_t)warp * c.tile_bufs * c.tile_stride);
+    int tsel = 0;
     Group<T> grp{reinterpret_cast<unsigned long long*>(smem_raw + c.off_red)};
     zero_code(c, sm, threadIdx.x, T);
     const int nvec = c.GS >> 4, n = c.n;
@@ -145,7 +147,7 @@ k_step_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint3
         if (obs != nullptr) {
             if (warp == 0) obs_publish(d, sm, lane, rec);
             __syncthreads();
-            obs_tiles(d, sm, obs, e, tile, warp, T / 32, lane);
+            obs_tiles(d, c, sm, obs, e, tile, tsel, warp, T / 32, lane);
             __syncthreads();
         }
         if (threadIdx.x == 0) ++env_steps;
@@ -187,7 +189,8 @@ k_obs_cta(const __grid_constant__ DevCfg c, const uint8_t* __restrict__ ground, 
     constexpr int T = kCtaThreads;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const Smem sm = carve(smem_raw, c);
-    float* tile = reinterpret_cast<float*>(smem_raw + c.off_tile + (size_t)warp * c.tile_stride);
+    float* tile = reinterpret_cast<float*>(smem_raw + c.off_tile + (size_t)warp * c.tile_bufs * c.tile_stride);
+    int tsel = 0;
     const D d{c};
     const int nvec = c.GS >> 4, n = c.n;
     for (long long e = blockIdx.x; e < c.N; e += gridDim.x) {
@@ -199,7 +202,7 @@ k_obs_cta(const __grid_constant__ DevCfg c, const uint8_t* __restrict__ ground, 
             obs_publish(d, sm, lane, rec);
         }
         __syncthreads();
-        obs_tiles(d, sm, obs, e, tile, warp, T / 32, lane);
+        obs_tiles(d, c, sm, obs, e, tile, tsel, warp, T / 32, lane);
     }
     tile_drain(lane);
 }
@@ -387,19 +390,22 @@ int drl_create(const drl_config* cfg, drl_env** out) {
     c.tile_drones = tile_drones_for(n, c.W2, e->warp_mode);
     c.ntiles = (n + c.tile_drones - 1) / c.tile_drones;
     c.tile_stride = round_up(c.tile_drones * cell_bytes, 128);
+    c.tile_bufs = 1;
     e->envs_per_warp = !e->warp_mode ? 1 : n <= 8 ? 4 : n <= 16 ? 2 : 1;
     const int Q = e->envs_per_warp;
-    c.off_code = Q * c.GS;
+    c.off_code = 2 * Q * c.GS;                      // two staging buffers of Q ground rows (warp step kernel)
     c.off_sdr = c.off_code + Q * round_up((int)G2, 16);
     c.off_sdf = c.off_sdr + 128;
     c.off_misc = c.off_sdf + 128;
-    c.off_red = c.off_misc + 16;
+    c.off_rec = c.off_misc + 16;                    // [2][32] staged drone records
+    c.off_key = c.off_rec + 256;                    // [2][Q][2] staged keys
+    c.off_red = c.off_key + 64;
     c.off_tile = round_up(c.off_red + 2 * (kCtaThreads / 32) * 8, 128);
     if (e->warp_mode) {
-        c.group_bytes = c.off_tile + c.tile_stride;
+        c.group_bytes = c.off_tile + c.tile_bufs * c.tile_stride;
         e->smem_bytes = c.group_bytes * kWarpsPerBlock;
     } else {
-        c.group_bytes = c.off_tile + c.tile_stride * (kCtaThreads / 32);
+        c.group_bytes = c.off_tile + c.tile_bufs * c.tile_stride * (kCtaThreads / 32);
         e->smem_bytes = c.group_bytes;
     }
     if (e->smem_bytes > (int)prop.sharedMemPerBlockOptin) {

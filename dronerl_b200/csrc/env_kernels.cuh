@@ -41,8 +41,9 @@ struct DevCfg {
     uint32_t mulG, mulW, mulW2, mulN;  // magic multipliers: x / d == umulhi(x, mul) for x*d < 2^32
     int tile_drones, ntiles;   // drones per obs tile, tiles per env
     int tile_stride;           // bytes reserved per obs tile buffer
+    int tile_bufs;             // tile buffers per warp (1, or 2 alternating)
     // shared-memory carve-up (bytes from the group's base)
-    int off_code, off_sdr, off_sdf, off_misc, off_red, off_tile;
+    int off_code, off_sdr, off_sdf, off_misc, off_rec, off_key, off_red, off_tile;
     int group_bytes;           // warp mode: bytes per warp; CTA mode: bytes per CTA
     long long N;               // local envs
 };
@@ -57,13 +58,14 @@ __device__ __forceinline__ uint32_t fdiv(uint32_t x, int d, uint32_t mul) { retu
 // hot shapes in so index arithmetic folds to constants and the window loops unroll.
 __host__ __device__ constexpr int tile_drones_for(int n, int W2, bool warp_mode) {
     const int cell_bytes = W2 * 24;
-    if (warp_mode) {
-        if (n * cell_bytes <= 12288) return n;
-        int td = 8192 / cell_bytes;
-        if (td > 1) td &= ~1;
-        return td < 1 ? 1 : td;
-    }
-    return (n >= 2 && 2 * cell_bytes <= 12288) ? 2 : 1;
+    if (n == 1 || 2 * cell_bytes > 12288) return 1;
+    if (!warp_mode) return 2;
+    // warp mode: the whole env when it fits, else an even number of drones so that tiles of an even-n
+    // env start 16-byte aligned (TMA bulk store)
+    if (n * cell_bytes <= 12288) return n;
+    int td = n & ~1;
+    while (td > 2 && td * cell_bytes > 8192) td -= 2;
+    return td;
 }
 
 template <int G_, int N_, int R_>
@@ -249,8 +251,13 @@ __device__ __forceinline__ void extract_ranks(Group<T>& grp, int tid, const D& d
 
 // ---- TMA bulk store of an obs tile ------------------------------------------------------------
 
-__device__ __forceinline__ void tile_wait_reusable(int lane) {
-    if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+// Two tile buffers alternate per warp; bulk groups complete in order, so "at most one group still
+// reading" means the buffer about to be refilled (used two stores ago) is free.
+__device__ __forceinline__ void tile_wait_reusable(int lane, int bufs) {
+    if (lane == 0) {
+        if (bufs > 1) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+        else asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+    }
     __syncwarp();
 }
 
@@ -286,28 +293,73 @@ __device__ __forceinline__ void tile_store(float* gdst, const float* ssrc, int b
 // non-zero entries are scattered: one lane per window ROW walks its W cells (ground class -> one
 // store), then one lane per (viewer, other drone) pair marks channels 0 and 4.
 template <class D>
-__device__ __forceinline__ void compose_tile(const D& d, const Smem& sm, int d0, int d1, float* tile, int lane) {
+__device__ __forceinline__ void compose_tile(const D& d, const Smem& sm, int d0, int d1, float* tile, int lane, int bufs) {
     const int nd = d1 - d0;
+    // ground value -> channel: 0 -> none, SKY 2 -> 5, STATION 3 -> 3, DROPZONE 4 -> 2, PACKET 5 -> 1
+    constexpr uint32_t kChan = (5u << 8) | (3u << 12) | (2u << 16) | (1u << 20);
+    const int W = d.W(), G = d.G();
+    const int rows = nd * W;
+    // lanes per window row: keep the warp busy when a tile has few rows
+    const int max_rows = d.tile_drones() * W;
+    const int lpr = max_rows <= 8 ? 4 : max_rows <= 16 ? 2 : 1;
+    const int items = rows * lpr;
+    // channel of cell wx of window row ``row`` (0 = nothing to store)
+    auto row_codes = [&](int item) -> uint32_t {
+        const int row = item / lpr, sl = item - row * lpr;
+        const int dd = (int)d.divW((uint32_t)row);
+        const int wy = row - dd * W;
+        const uint32_t rec = sm.sdr[d0 + dd];
+        const int gy = (int)((rec >> 8) & 0xFFu) + wy - d.r();
+        const int gx0 = (int)(rec & 0xFFu) - d.r();
+        uint32_t packed = 0;
+        if ((unsigned)gy >= (unsigned)G) {
+            for (int wx = sl, j = 0; wx < W; wx += lpr, ++j) packed |= 5u << (3 * j);     // the whole row is wall
+        } else {
+            const uint8_t* grow = sm.sg + gy * G;
+            for (int wx = sl, j = 0; wx < W; wx += lpr, ++j) {
+                const int gx = gx0 + wx;
+                const uint32_t g = (unsigned)gx < (unsigned)G ? grow[gx] : (uint32_t)SKY;
+                packed |= ((kChan >> (4u * g)) & 7u) << (3 * j);
+            }
+        }
+        return packed;
+    };
+    auto row_emit = [&](int item, uint32_t packed) {
+        const int row = item / lpr, sl = item - row * lpr;
+        float* o = tile + row * W * 6;
+        for (int wx = sl; wx < W; wx += lpr, packed >>= 3) {
+            const uint32_t ch = packed & 7u;
+            if (ch) o[wx * 6 + ch] = 1.0f;
+        }
+    };
+    // Window analysis does not touch the tile, so it runs BEFORE waiting for the previous bulk store to
+    // release the buffer (up to two rows per lane, ten 3-bit codes per row, kept in registers).
+    const bool packed_path = items <= 64 && (W + lpr - 1) / lpr <= 10;
+    uint32_t p0 = 0, p1 = 0;
+    if (packed_path) {
+        if (lane < items) p0 = row_codes(lane);
+        if (lane + 32 < items) p1 = row_codes(lane + 32);
+    }
+    tile_wait_reusable(lane, bufs);
     const int vecs = (nd * d.W2() * 24 + 15) >> 4;          // tile buffers are padded to 128 B
     float4* t4 = reinterpret_cast<float4*>(tile);
     for (int i = lane; i < vecs; i += 32) t4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     __syncwarp();
-    // ground value -> channel: 0 -> none, SKY 2 -> 5, STATION 3 -> 3, DROPZONE 4 -> 2, PACKET 5 -> 1
-    constexpr uint32_t kChan = (5u << 8) | (3u << 12) | (2u << 16) | (1u << 20);
-    const int rows = nd * d.W();
-    for (int row = lane; row < rows; row += 32) {
-        const int dd = (int)d.divW((uint32_t)row);
-        const int wy = row - dd * d.W();
-        const uint32_t rec = sm.sdr[d0 + dd];
-        const int gy = (int)((rec >> 8) & 0xFFu) + wy - d.r();
-        int gx = (int)(rec & 0xFFu) - d.r();
-        float* o = tile + row * d.W() * 6;
-        if ((unsigned)gy >= (unsigned)d.G()) {
-            for (int wx = 0; wx < d.W(); ++wx) o[wx * 6 + 5] = 1.0f;          // the whole row is wall
-        } else {
-            const uint8_t* grow = sm.sg + gy * d.G();
-            for (int wx = 0; wx < d.W(); ++wx, ++gx) {
-                const uint32_t g = (unsigned)gx < (unsigned)d.G() ? grow[gx] : (uint32_t)SKY;
+    if (packed_path) {
+        if (lane < items) row_emit(lane, p0);
+        if (lane + 32 < items) row_emit(lane + 32, p1);
+    } else {
+        for (int item = lane; item < items; item += 32) {      // big windows / many rows: cell by cell
+            const int row = item / lpr, sl = item - row * lpr;
+            const int dd = (int)d.divW((uint32_t)row);
+            const int wy = row - dd * W;
+            const uint32_t rec = sm.sdr[d0 + dd];
+            const int gy = (int)((rec >> 8) & 0xFFu) + wy - d.r();
+            const int gx0 = (int)(rec & 0xFFu) - d.r();
+            float* o = tile + row * W * 6;
+            for (int wx = sl; wx < W; wx += lpr) {
+                const int gx = gx0 + wx;
+                const uint32_t g = ((unsigned)gy < (unsigned)G && (unsigned)gx < (unsigned)G) ? sm.sg[gy * G + gx] : (uint32_t)SKY;
                 const uint32_t ch = (kChan >> (4u * g)) & 7u;
                 if (ch) o[wx * 6 + ch] = 1.0f;
             }
@@ -322,8 +374,8 @@ __device__ __forceinline__ void compose_tile(const D& d, const Smem& sm, int d0,
         const uint32_t rv = sm.sdr[d0 + dd], rj = sm.sdr[j];
         const int dx = (int)(rj & 0xFFu) - (int)(rv & 0xFFu) + d.r();
         const int dy = (int)((rj >> 8) & 0xFFu) - (int)((rv >> 8) & 0xFFu) + d.r();
-        if (((rj >> 17) & 1u) && (unsigned)dx < (unsigned)d.W() && (unsigned)dy < (unsigned)d.W()) {
-            float* o = tile + ((dd * d.W2() + dy * d.W() + dx) * 6);
+        if (((rj >> 17) & 1u) && (unsigned)dx < (unsigned)W && (unsigned)dy < (unsigned)W) {
+            float* o = tile + ((dd * d.W2() + dy * W + dx) * 6);
             o[0] = 1.0f;
             o[4] = sm.sdf[j];
         }
@@ -348,17 +400,19 @@ __device__ __forceinline__ void obs_publish(const D& d, const Smem& sm, int lane
     }
 }
 
-// Warp-level: compose + store every tile t = first, first + step, ... of env ``e``.
+// Warp-level: compose + store every tile t = first, first + step, ... of env ``e``.  ``tile`` points at
+// the warp's two buffers (tile_stride bytes apart); ``tsel`` alternates between them across calls.
 template <class D>
-__device__ __forceinline__ void obs_tiles(const D& d, const Smem& sm, float* obs, long long e, float* tile,
-                                          int first, int step, int lane) {
+__device__ __forceinline__ void obs_tiles(const D& d, const DevCfg& c, const Smem& sm, float* obs, long long e, float* tile,
+                                          int& tsel, int first, int step, int lane) {
     for (int t = first; t < d.ntiles(); t += step) {
         const int d0 = t * d.tile_drones();
         const int d1 = min(d.n(), d0 + d.tile_drones());
-        tile_wait_reusable(lane);
-        compose_tile(d, sm, d0, d1, tile, lane);
+        float* buf = tile + tsel * (c.tile_stride >> 2);
+        tsel ^= (c.tile_bufs - 1);
+        compose_tile(d, sm, d0, d1, buf, lane, c.tile_bufs);
         float* gdst = obs + ((size_t)e * d.n() + d0) * (size_t)(d.W2() * 6);
-        tile_store(gdst, tile, (d1 - d0) * d.W2() * 24, lane);
+        tile_store(gdst, buf, (d1 - d0) * d.W2() * 24, lane);
     }
 }
 

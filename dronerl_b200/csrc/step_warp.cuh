@@ -54,6 +54,7 @@ __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsi
     const int k = c.k_spawn;
     Stats st;
     unsigned env_steps = 0;
+    int tsel = 0;
 
     GroupInputs nxt = {};
     auto prefetch = [&](long long g) {
@@ -297,7 +298,7 @@ __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsi
                 smq.sdr = sdr + q * S;
                 smq.sdf = sdf + q * S;
                 smq.misc = nullptr;
-                obs_tiles(d, smq, obs, e0 + q, tile, 0, 1, lane);
+                obs_tiles(d, c, smq, obs, e0 + q, tile, tsel, 0, 1, lane);
             }
         }
         env_steps += nq;
