@@ -40,6 +40,10 @@ def parse_args():
     ap.add_argument('--grid', type=int, default=G)
     ap.add_argument('--drones', type=int, default=N_DRONES)
     ap.add_argument('--radius', type=int, default=RADIUS)
+    ap.add_argument('--packets-factor', type=int, default=3)
+    ap.add_argument('--dropzones-factor', type=int, default=2)
+    ap.add_argument('--stations-factor', type=int, default=2)
+    ap.add_argument('--skyscrapers-factor', type=int, default=3)
     ap.add_argument('--cpu-sample-envs', type=int, default=1 << 16)
     ap.add_argument('--cpu-seconds', type=float, default=12.0)
     ap.add_argument('--no-cpu-baseline', action='store_true')
@@ -47,8 +51,15 @@ def parse_args():
     return ap.parse_args()
 
 
+def factors(a):
+    return dict(packets_factor=a.packets_factor, dropzones_factor=a.dropzones_factor, stations_factor=a.stations_factor,
+                skyscrapers_factor=a.skyscrapers_factor)
+
+
 def workload_name(a):
-    return (f'default grid G={a.grid} n_drones={a.drones} WindowedGridView r={a.radius}, random-agent rollout, '
+    kind = 'default grid' if (a.grid, a.drones, a.radius) == (G, N_DRONES, RADIUS) else 'grid'
+    f = '' if tuple(factors(a).values()) == (3, 2, 2, 3) else ' factors pk/dz/st/sky=%d/%d/%d/%d' % tuple(factors(a).values())
+    return (f'{kind} G={a.grid} n_drones={a.drones} WindowedGridView r={a.radius}{f}, random-agent rollout, '
             f'{a.envs_per_gpu} envs/GPU, reset every {RESET_EVERY} steps')
 
 
@@ -115,7 +126,7 @@ def cpu_rollout_rate(a, seconds, steps=None, warmup=1):
     from oracle import c_oracle as C
     from oracle import env_ref as E
     C.build()
-    p = E.Params(grid_size=a.grid, n_drones=a.drones, window_radius=a.radius)
+    p = E.Params(grid_size=a.grid, n_drones=a.drones, window_radius=a.radius, **factors(a))
     N = a.cpu_sample_envs
     cores = len(os.sched_getaffinity(0))
     threads = min(cores, C.max_threads()) if C.max_threads() > 0 else cores
@@ -183,7 +194,7 @@ def run_b200(a):
         dist.init_process_group('nccl', device_id=torch.device('cuda', local_rank))
     n_gpus = world
 
-    p = drl.DroneEnvParams(grid_size=a.grid, n_drones=a.drones, window_radius=a.radius)
+    p = drl.DroneEnvParams(grid_size=a.grid, n_drones=a.drones, window_radius=a.radius, **factors(a))
     N_local = a.envs_per_gpu
     N_global = N_local * world
     ro = ShardedRollout(p, N_global, rank, world, seed=0, reset_every=RESET_EVERY)
@@ -241,11 +252,13 @@ def run_b200(a):
         peak, peak_src = 6650.0, 'fallback (B200_PROFILING.md)'
     traffic = None
     tpath = os.path.join(ROOT, 'profiles', 'step_kernel_traffic.json')
-    if os.path.exists(tpath):
+    is_default = (a.grid, a.drones, a.radius, N_local) == (G, N_DRONES, RADIUS, 1 << 20) and tuple(factors(a).values()) == (3, 2, 2, 3)
+    if os.path.exists(tpath) and is_default:      # ncu --set full capture of exactly this launch shape (profiles/)
         try:
             traffic = json.load(open(tpath)).get('dram_bytes_per_launch')
         except Exception:
             traffic = None
+    kernel_name = ('k_step_warp' if a.grid * a.grid <= 128 else 'k_step_cta') + ' (fused step+get_obs)'
 
     # ---- e2e: the C-ABI call with HOST buffers (actions in, rewards+dones out), per step -------------
     e2e = None
@@ -294,13 +307,14 @@ def run_b200(a):
             'dtype': 'u8', 'data': 'synthetic',
             'config': {'workload': workload_name(a), 'num_envs_global': N_global, 'grid_size': a.grid,
                        'n_drones': a.drones, 'window_radius': a.radius, 'parallelism': f'env-sharded x{n_gpus}',
-                       'l2': 'inputs_exceed_l2 (state 113 MB read+written, obs 4.9 GB written per step per GPU)'
-                             if N_local >= (1 << 20) else 'working set per step = %d MB' % (B_env * N_local >> 20),
+                       'l2': ('inputs_exceed_l2' if B_env * N_local > (256 << 20) else 'working_set_fits_l2') +
+                             ' (state %d MB read+written, obs %d MB written per step per GPU; L2 is 126 MB)' % (
+                                 (a.grid * a.grid + 4 * a.drones) * N_local >> 20, 24 * a.drones * (2 * a.radius + 1) ** 2 * N_local >> 20),
                        'env_steps_per_s': value / p.n_drones, 'algorithmic_bytes_per_env_step': B_env,
                        'episode_stats': {k: stats[k] for k in ('env_steps', 'dones', 'deliveries', 'pickups', 'resets',
                                                                'mean_reward_per_drone_step')}},
             'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s', 'frac': achieved / peak,
-                         'traffic': traffic, 'kernel': 'k_step_warp (fused step+get_obs)', 'kernel_ms': k_ms,
+                         'traffic': traffic, 'kernel': kernel_name, 'kernel_ms': k_ms,
                          'peak_source': peak_src, 'algorithmic_bytes_per_launch': B_env * N_local},
             'clocks': clocks, 'gpu_launches': launches,
         }

@@ -8,5 +8,6 @@ from .params import Action, Object, DroneEnvParams
 from .state import DroneEnvState
 from .env import DeliveryDrones
 from . import random
+from . import gym_api
 
-__all__ = ['Action', 'Object', 'DroneEnvParams', 'DroneEnvState', 'DeliveryDrones', 'random']
+__all__ = ['Action', 'Object', 'DroneEnvParams', 'DroneEnvState', 'DeliveryDrones', 'random', 'gym_api']

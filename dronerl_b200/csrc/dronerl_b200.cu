@@ -313,6 +313,23 @@ static obs_fn pick_obs(const drl_env* e) {
     return (obs_fn)k_obs_cta<DynDims>;
 }
 
+// Launch through cudaLaunchKernel so the status is THIS launch's: the <<<>>> form reports through the
+// thread's last-error slot, which a caller's earlier, unrelated runtime call (e.g. a pointer-attribute
+// probe inside the tensor library) may have left set.
+template <class... Args>
+static int launch(drl_env* env, const char* what, const void* fn, int grid, int threads, int smem, void* stream,
+                  Args... args) {
+    void* argv[] = {(void*)&args...};
+    (void)cudaGetLastError();
+    cudaError_t ce = cudaLaunchKernel(fn, dim3((unsigned)grid), dim3((unsigned)threads), argv, (size_t)smem,
+                                      (cudaStream_t)stream);
+    if (ce != cudaSuccess) {
+        (void)cudaGetLastError();
+        return fail(env, DRL_ECUDA, "launch of %s failed: CUDA error %lld", what, (long long)ce);
+    }
+    return DRL_OK;
+}
+
 extern "C" {
 
 int drl_abi_version(void) { return DRL_ABI_VERSION; }
@@ -421,7 +438,10 @@ int drl_create(const drl_config* cfg, drl_env** out) {
     for (int i = 0; i < 3; ++i) {
         const long long per_cta = e->warp_mode ? (long long)kWarpsPerBlock * (i == 0 ? Q : 1) : 1;
         const long long units = (c.N + per_cta - 1) / per_cta;
-        cudaError_t ce = cudaFuncSetAttribute(fns[i], cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem_bytes);
+        // the attribute belongs to the FUNCTION, which handles of other shapes share: always grant the device's
+        // opt-in maximum (a smaller value set by a later handle would make this handle's launches invalid)
+        cudaError_t ce = cudaFuncSetAttribute(fns[i], cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)prop.sharedMemPerBlockOptin);
         int per_sm = 0;
         if (ce == cudaSuccess) ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fns[i], threads, e->smem_bytes);
         if (ce != cudaSuccess || per_sm < 1) {
@@ -477,18 +497,11 @@ int drl_bind_state(drl_env* env, void* d_ground, void* d_drones) {
     return DRL_OK;
 }
 
-static int check_launch(drl_env* env, const char* what) {
-    cudaError_t ce = cudaGetLastError();
-    if (ce != cudaSuccess) return fail(env, DRL_ECUDA, "launch of %s failed: CUDA error %lld", what, (long long)ce);
-    return DRL_OK;
-}
-
 int drl_split_n(const uint32_t key[2], int64_t num, int64_t offset, int64_t count, void* d_out, void* stream) {
     if (!key || !d_out || num < 1 || offset < 0 || count < 0 || offset + count > num || num > (1ll << 30)) return DRL_EINVAL;
     if (count == 0) return DRL_OK;
-    k_split_keys<<<(unsigned)((2 * count + 255) / 256), 256, 0, (cudaStream_t)stream>>>(key[0], key[1], num, offset, count,
-                                                                                       (uint32_t*)d_out);
-    return cudaGetLastError() == cudaSuccess ? DRL_OK : DRL_ECUDA;
+    return launch(nullptr, "split kernel", (const void*)k_split_keys, (int)((2 * count + 255) / 256), 256, 0, stream, key[0],
+                  key[1], (long long)num, (long long)offset, (long long)count, (uint32_t*)d_out);
 }
 
 int drl_randint_n(const uint32_t key[2], int64_t total, int64_t first, int64_t count, int32_t maxval, void* d_out,
@@ -502,9 +515,8 @@ int drl_randint_n(const uint32_t key[2], int64_t total, int64_t first, int64_t c
     const uint32_t span = (uint32_t)maxval;
     uint32_t mult = 65536u % span;
     mult = (mult * mult) % span;
-    k_randint<<<(unsigned)((count + 255) / 256), 256, 0, (cudaStream_t)stream>>>(k1[0], k1[1], k2[0], k2[1], total, first,
-                                                                                count, span, mult, (int8_t*)d_out);
-    return cudaGetLastError() == cudaSuccess ? DRL_OK : DRL_ECUDA;
+    return launch(nullptr, "randint kernel", (const void*)k_randint, (int)((count + 255) / 256), 256, 0, stream, k1[0], k1[1],
+                  k2[0], k2[1], (long long)total, (long long)first, (long long)count, span, mult, (int8_t*)d_out);
 }
 
 int drl_split_keys(drl_env* env, const uint32_t key[2], void* d_keys_out, void* stream) {
@@ -528,9 +540,8 @@ int drl_reset(drl_env* env, const void* d_keys, void* stream) {
     if (!env->d_ground) return fail(env, DRL_ESTATE, "drl_reset: state not bound (call drl_bind_state)%s");
     CUDA_TRY(env, cudaSetDevice(env->cfg.device));
     const int threads = env->warp_mode ? kWarpsPerBlock * 32 : kCtaThreads;
-    pick_reset(env)<<<env->grid_reset, threads, env->smem_bytes, (cudaStream_t)stream>>>(
-        env->dc, env->d_ground, env->d_drones, (const uint32_t*)d_keys, env->d_stats);
-    return check_launch(env, "reset kernel");
+    return launch(env, "reset kernel", (const void*)pick_reset(env), env->grid_reset, threads, env->smem_bytes, stream, env->dc,
+                  env->d_ground, env->d_drones, (const uint32_t*)d_keys, env->d_stats);
 }
 
 int drl_step(drl_env* env, const void* d_keys, const void* d_actions, void* d_rewards, void* d_dones, void* d_obs,
@@ -540,10 +551,9 @@ int drl_step(drl_env* env, const void* d_keys, const void* d_actions, void* d_re
     if ((uintptr_t)d_obs & 7) return fail(env, DRL_EINVAL, "drl_step: obs must be 8-byte aligned%s");
     CUDA_TRY(env, cudaSetDevice(env->cfg.device));
     const int threads = env->warp_mode ? kWarpsPerBlock * 32 : kCtaThreads;
-    pick_step(env)<<<env->grid_step, threads, env->smem_bytes, (cudaStream_t)stream>>>(
-        env->dc, env->d_ground, env->d_drones, (const uint32_t*)d_keys, (const int8_t*)d_actions, (float*)d_rewards,
-        (uint8_t*)d_dones, (float*)d_obs, env->d_stats);
-    return check_launch(env, "step kernel");
+    return launch(env, "step kernel", (const void*)pick_step(env), env->grid_step, threads, env->smem_bytes, stream, env->dc,
+                  env->d_ground, env->d_drones, (const uint32_t*)d_keys, (const int8_t*)d_actions, (float*)d_rewards,
+                  (uint8_t*)d_dones, (float*)d_obs, env->d_stats);
 }
 
 int drl_get_obs(drl_env* env, void* d_obs, void* stream) {
@@ -552,9 +562,8 @@ int drl_get_obs(drl_env* env, void* d_obs, void* stream) {
     if ((uintptr_t)d_obs & 7) return fail(env, DRL_EINVAL, "drl_get_obs: obs must be 8-byte aligned%s");
     CUDA_TRY(env, cudaSetDevice(env->cfg.device));
     const int threads = env->warp_mode ? kWarpsPerBlock * 32 : kCtaThreads;
-    pick_obs(env)<<<env->grid_obs, threads, env->smem_bytes, (cudaStream_t)stream>>>(env->dc, env->d_ground, env->d_drones,
-                                                                                  (float*)d_obs);
-    return check_launch(env, "obs kernel");
+    return launch(env, "obs kernel", (const void*)pick_obs(env), env->grid_obs, threads, env->smem_bytes, stream, env->dc,
+                  (const uint8_t*)env->d_ground, (const uint32_t*)env->d_drones, (float*)d_obs);
 }
 
 static int ensure_scratch(drl_env* env) {
