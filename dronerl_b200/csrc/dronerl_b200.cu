@@ -72,7 +72,7 @@ k_reset_warp(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uin
         if (lane < nvec) reinterpret_cast<uint4*>(sm.sg)[lane] = make_uint4(0, 0, 0, 0);
         __syncwarp();
         uint32_t rec = 0;
-        env_reset<32, NB>(grp, c, DynDims{c}, sm, rec, kk.x, kk.y);
+        env_reset<32, NB>(grp, c, DynDims{c}, sm, Sel{}, rec, kk.x, kk.y);
         if (lane < nvec) reinterpret_cast<uint4*>(ground + e * c.GS)[lane] = reinterpret_cast<const uint4*>(sm.sg)[lane];
         if (lane < n) drones[e * n + lane] = rec;
         ++resets;
@@ -118,6 +118,7 @@ k_step_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint3
     float* tile = reinterpret_cast<float*>(smem_raw + c.off_tile + (size_t)warp * c.tile_bufs * c.tile_stride);
     int tsel = 0;
     Group<T> grp{reinterpret_cast<unsigned long long*>(smem_raw + c.off_red)};
+    const Sel sel = carve_sel(smem_raw, c);
     zero_code(c, sm, threadIdx.x, T);
     const int nvec = c.GS >> 4, n = c.n;
     Stats st;
@@ -140,7 +141,7 @@ k_step_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint3
         }
         const uint2 kk = *reinterpret_cast<const uint2*>(keys + 2 * e);
         const int F0 = grp.sum(zc) - (c.GS - c.G2);     // block-wide: also publishes the ground stores
-        env_step<T, NB>(grp, c, d, sm, validm, F0, rec, act, kk.x, kk.y, rewards + e * n, dones + e * n, st);
+        env_step<T, NB>(grp, c, d, sm, sel, validm, F0, rec, act, kk.x, kk.y, rewards + e * n, dones + e * n, st);
         for (int i = threadIdx.x; i < nvec; i += T)
             reinterpret_cast<uint4*>(ground + e * c.GS)[i] = reinterpret_cast<const uint4*>(sm.sg)[i];
         if (threadIdx.x < n) drones[e * n + threadIdx.x] = rec;
@@ -164,6 +165,7 @@ k_reset_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint
     constexpr int T = kCtaThreads;
     const Smem sm = carve(smem_raw, c);
     Group<T> grp{reinterpret_cast<unsigned long long*>(smem_raw + c.off_red)};
+    const Sel sel = carve_sel(smem_raw, c);
     const int nvec = c.GS >> 4, n = c.n;
     unsigned resets = 0;
     for (long long e = blockIdx.x; e < c.N; e += gridDim.x) {
@@ -171,7 +173,7 @@ k_reset_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint
         for (int i = threadIdx.x; i < nvec; i += T) reinterpret_cast<uint4*>(sm.sg)[i] = make_uint4(0, 0, 0, 0);
         __syncthreads();
         uint32_t rec = 0;
-        env_reset<T, NB>(grp, c, DynDims{c}, sm, rec, kk.x, kk.y);
+        env_reset<T, NB>(grp, c, DynDims{c}, sm, sel, rec, kk.x, kk.y);
         for (int i = threadIdx.x; i < nvec; i += T)
             reinterpret_cast<uint4*>(ground + e * c.GS)[i] = reinterpret_cast<const uint4*>(sm.sg)[i];
         if (threadIdx.x < n) drones[e * n + threadIdx.x] = rec;
@@ -417,7 +419,13 @@ int drl_create(const drl_config* cfg, drl_env** out) {
     c.off_rec = c.off_misc + 16;                    // [2][32] staged drone records
     c.off_key = c.off_rec + 256;                    // [2][Q][2] staged keys
     c.off_red = c.off_key + 64;
-    c.off_tile = round_up(c.off_red + 2 * (kCtaThreads / 32) * 8, 128);
+    c.off_sel = round_up(c.off_red + 2 * (kCtaThreads / 32) * 8, 16);
+    c.sel_maxj = c.k_spawn > n ? c.k_spawn : n;
+    for (int i = 0; i < 4; ++i) c.sel_maxj = c.k_reset[i] > c.sel_maxj ? c.k_reset[i] : c.sel_maxj;
+    c.sel_cap = c.sel_maxj + 256;                   // J keys plus a generous few histogram bins' worth
+    // CTA mode only: histogram [256] + counters [4] | key list [cap] | rank -> position table [maxj]
+    const int sel_bytes = e->warp_mode ? 0 : 1040 + c.sel_cap * 8 + round_up(c.sel_maxj * 2, 16);
+    c.off_tile = round_up(c.off_sel + sel_bytes, 128);
     if (e->warp_mode) {
         c.group_bytes = c.off_tile + c.tile_bufs * c.tile_stride;
         e->smem_bytes = c.group_bytes * kWarpsPerBlock;

@@ -43,7 +43,8 @@ struct DevCfg {
     int tile_stride;           // bytes reserved per obs tile buffer
     int tile_bufs;             // tile buffers per warp (1, or 2 alternating)
     // shared-memory carve-up (bytes from the group's base)
-    int off_code, off_sdr, off_sdf, off_misc, off_rec, off_key, off_red, off_tile;
+    int off_code, off_sdr, off_sdf, off_misc, off_rec, off_key, off_red, off_sel, off_tile;
+    int sel_cap, sel_maxj;     // CTA mode: capacity of the selection list, of the rank -> position table
     int group_bytes;           // warp mode: bytes per warp; CTA mode: bytes per CTA
     long long N;               // local envs
 };
@@ -249,6 +250,98 @@ __device__ __forceinline__ void extract_ranks(Group<T>& grp, int tid, const D& d
     }
 }
 
+// ---- CTA mode: top-J by threshold selection ------------------------------------------------------
+//
+// Rank-by-rank arg-max costs a block-wide reduction (two barriers) per rank, which dominates a step on
+// big grids (ncu: 69 % of the instructions at 64x64 / 32 drones).  Instead: histogram the candidates'
+// 23-bit mantissas by their top 8 bits, find the bin where the count from the top reaches J, gather
+// everything at or above that bin (J plus about one bin's worth of keys) and rank those few keys by
+// counting.  Exact, ties included, because the final ranking compares full (mantissa + 1, G2 - cell)
+// keys.  The -inf tail (fewer candidates than J) and a pathological overflow of the list take the
+// serial path.
+struct Sel {
+    uint32_t* hist;             // [256]
+    uint32_t* cnt;              // [4]
+    unsigned long long* list;   // [cap]
+    uint16_t* pos;              // [maxj]  rank -> flat cell
+    int cap;
+};
+
+__device__ __forceinline__ Sel carve_sel(unsigned char* base, const DevCfg& c) {
+    Sel s;
+    s.hist = reinterpret_cast<uint32_t*>(base + c.off_sel);
+    s.cnt = s.hist + 256;
+    s.list = reinterpret_cast<unsigned long long*>(base + c.off_sel + 1040);
+    s.pos = reinterpret_cast<uint16_t*>(base + c.off_sel + 1040 + (size_t)c.sel_cap * 8);
+    s.cap = c.sel_cap;
+    return s;
+}
+
+// sel.pos[0 .. J) = positions of jax.lax.top_k(log(cand) + noise, J) in rank order; ends with a barrier.
+template <int T, int NB, class D>
+__device__ __forceinline__ void rank_positions(Group<T>& grp, const D& d, const Sel& sel, int tid,
+                                               const uint32_t (&mant)[2 * NB], uint32_t candm, uint32_t validm, int J) {
+    static_assert(T >= 256 && T % 32 == 0, "CTA mode");
+    const int lane = tid & 31;
+    for (int i = tid; i < 256; i += T) sel.hist[i] = 0u;
+    if (tid == 0) sel.cnt[0] = 0u;
+    __syncthreads();
+#pragma unroll
+    for (int s = 0; s < 2 * NB; ++s)
+        if ((candm >> s) & 1u) atomicAdd(&sel.hist[mant[s] >> 15], 1u);
+    __syncthreads();
+    // every warp finds the threshold bin for itself (same histogram, same answer, no broadcast barrier)
+    uint32_t h[8];
+    {
+        const uint4 a = reinterpret_cast<const uint4*>(sel.hist)[2 * lane], b = reinterpret_cast<const uint4*>(sel.hist)[2 * lane + 1];
+        h[0] = a.x; h[1] = a.y; h[2] = a.z; h[3] = a.w; h[4] = b.x; h[5] = b.y; h[6] = b.z; h[7] = b.w;
+    }
+    const uint32_t local = h[0] + h[1] + h[2] + h[3] + h[4] + h[5] + h[6] + h[7];
+    uint32_t suf = local;                          // inclusive suffix sum over lanes
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const uint32_t v = __shfl_down_sync(FULL, suf, off);
+        if (lane + off < 32) suf += v;
+    }
+    const uint32_t total = __shfl_sync(FULL, suf, 0);
+    bool fast = total >= (uint32_t)J;
+    int bstar = 0;
+    uint32_t m = 0;
+    if (fast) {
+        const int L = 31 - __clz(__ballot_sync(FULL, suf >= (uint32_t)J));
+        uint32_t acc = suf - local, cge = 0;
+        int b = -1;
+#pragma unroll
+        for (int i = 7; i >= 0; --i) {
+            acc += h[i];
+            if (b < 0 && acc >= (uint32_t)J) { b = 8 * lane + i; cge = acc; }
+        }
+        bstar = __shfl_sync(FULL, b, L);
+        m = __shfl_sync(FULL, cge, L);
+        fast = m <= (uint32_t)sel.cap;
+    }
+    if (fast) {
+#pragma unroll
+        for (int s = 0; s < 2 * NB; ++s)
+            if (((candm >> s) & 1u) && (int)(mant[s] >> 15) >= bstar) {
+                const uint32_t i = atomicAdd(sel.cnt, 1u);
+                sel.list[i] = ((unsigned long long)(mant[s] + 1u) << 16) | (unsigned)(d.G2() - slot_cell<T>(tid, s, d.H()));
+            }
+        __syncthreads();
+        for (int t = tid; t < (int)m; t += T) {
+            const unsigned long long key = sel.list[t];
+            int r = 0;
+            for (int u = 0; u < (int)m; ++u) r += sel.list[u] > key;
+            if (r < J) sel.pos[r] = (uint16_t)(d.G2() - (int)(key & 0xFFFFull));
+        }
+    } else {
+        extract_ranks<T, NB>(grp, tid, d, mant, candm, validm, J, [&](int j, int pos) {
+            if (tid == 0) sel.pos[j] = (uint16_t)pos;
+        });
+    }
+    __syncthreads();
+}
+
 // ---- TMA bulk store of an obs tile ------------------------------------------------------------
 
 // Two tile buffers alternate per warp; bulk groups complete in order, so "at most one group still
@@ -423,7 +516,7 @@ __device__ __forceinline__ void obs_tiles(const D& d, const DevCfg& c, const Sme
 // Drone i lives in lane i of warp 0 of the group (``rec``/``act`` valid there).
 // Postconditions: sm.sg holds the new ground, ``rec`` the new drone record, rewards/dones written.
 template <int T, int NB, class D>
-__device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const D& d, const Smem& sm, uint32_t validm, int F0,
+__device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const D& d, const Smem& sm, const Sel& sel, uint32_t validm, int F0,
                                          uint32_t& rec, int act, uint32_t k0, uint32_t k1, float* rewards_e,
                                          uint8_t* dones_e, Stats& st) {
     constexpr bool kWarp = Group<T>::kWarp;
@@ -539,9 +632,9 @@ __device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const D
         scan_free();
         ensure_noise();
         const int J = F1 < k ? k : 32 - __clz(mP);
-        extract_ranks<T, NB>(grp, tid, d, mant, freem, validm, J, [&](int j, int pos) {
-            if (tid == 0) sm.sg[pos] = (j < n && ((mP >> j) & 1u)) ? PACKET : 0;
-        });
+        rank_positions<T, NB>(grp, d, sel, tid, mant, freem, validm, J);
+        // grid.at[pos].set(fill): rank j takes fill[j]; the cells are distinct, so all ranks write at once
+        for (int j = tid; j < J; j += T) sm.sg[sel.pos[j]] = (j < n && ((mP >> j) & 1u)) ? PACKET : 0;
     }
     // S9 dropzone respawn (env.py:205-212): same spawn_key, hence the same noise
     if (mD != 0 || F1 - __popc(mP) < k) {
@@ -553,9 +646,8 @@ __device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const D
             if (F2 < k) capture_oldsky();
             ensure_noise();
             const int J = F2 < k ? k : 32 - __clz(mD);
-            extract_ranks<T, NB>(grp, tid, d, mant, freem, validm, J, [&](int j, int pos) {
-                if (tid == 0) sm.sg[pos] = (j < n && ((mD >> j) & 1u)) ? DROPZONE : 0;
-            });
+            rank_positions<T, NB>(grp, d, sel, tid, mant, freem, validm, J);
+            for (int j = tid; j < J; j += T) sm.sg[sel.pos[j]] = (j < n && ((mD >> j) & 1u)) ? DROPZONE : 0;
         }
     }
 
@@ -574,18 +666,18 @@ __device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const D
             if (((validm >> s) & 1u) && !((oldsky >> s) & 1u) && cell != G2 - 1 && sm.code[cell] == 0) candm |= 1u << s;
         }
         noise_mantissas<T, NB>(tid, d, sk0, sk1, mant);
-        extract_ranks<T, NB>(grp, tid, d, mant, candm, validm, 32 - __clz(mDone), [&](int j, int pos) {
-            if (drone_warp && lane == j && done) {
-                x = (int)d.divG((uint32_t)pos);    // rank i -> drone i: x = pos // G, y = pos % G
-                y = pos - x * G;
-                if (sm.sg[pos] == PACKET) {                 // package_mask[new_x, new_y]: flat index x*G+y == pos
-                    carry = 1;
-                    sm.sg[pos] = 0;
-                    st.respawn_pickups += 1;
-                }
-            }
-        });
+        rank_positions<T, NB>(grp, d, sel, tid, mant, candm, validm, 32 - __clz(mDone));
         if (drone_warp && surv) sm.code[x * G + y] = 0;     // restore the all-zero invariant
+        if (drone_warp && done) {
+            const int pos = sel.pos[lane];
+            x = (int)d.divG((uint32_t)pos);        // rank i -> drone i: x = pos // G, y = pos % G
+            y = pos - x * G;
+            if (sm.sg[pos] == PACKET) {                     // package_mask[new_x, new_y]: flat index x*G+y == pos
+                carry = 1;
+                sm.sg[pos] = 0;
+                st.respawn_pickups += 1;
+            }
+        }
     }
     if (drone_warp)
         rec = (uint32_t)x | ((uint32_t)y << 8) | ((uint32_t)carry << 16) | ((uint32_t)ch << 24);
@@ -594,8 +686,8 @@ __device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const D
 
 // ---- one env reset (env.py:89-135) -------------------------------------------------------------
 template <int T, int NB, class D>
-__device__ __forceinline__ void env_reset(Group<T>& grp, const DevCfg& c, const D& d, const Smem& sm, uint32_t& rec, uint32_t k0,
-                                          uint32_t k1) {
+__device__ __forceinline__ void env_reset(Group<T>& grp, const DevCfg& c, const D& d, const Smem& sm, const Sel& sel,
+                                          uint32_t& rec, uint32_t k0, uint32_t k1) {
     constexpr bool kWarp = Group<T>::kWarp;
     const int tid = Group<T>::tid();
     const int lane = threadIdx.x & 31;
@@ -615,9 +707,14 @@ __device__ __forceinline__ void env_reset(Group<T>& grp, const DevCfg& c, const 
             if (((validm >> s) & 1u) && sm.sg[slot_cell<T>(tid, s, d.H())] == 0) freem |= 1u << s;
         noise_mantissas<T, NB>(tid, d, sk0, sk1, mant);
         const int obj = objs[t];
-        extract_ranks<T, NB>(grp, tid, d, mant, freem, validm, c.k_reset[t], [&](int, int pos) {
-            if (tid == 0) sm.sg[pos] = (uint8_t)obj;
-        });
+        if constexpr (kWarp) {
+            extract_ranks<T, NB>(grp, tid, d, mant, freem, validm, c.k_reset[t], [&](int, int pos) {
+                if (tid == 0) sm.sg[pos] = (uint8_t)obj;
+            });
+        } else {
+            rank_positions<T, NB>(grp, d, sel, tid, mant, freem, validm, c.k_reset[t]);
+            for (int j = tid; j < c.k_reset[t]; j += T) sm.sg[sel.pos[j]] = (uint8_t)obj;
+        }
         Group<T>::sync();
     }
     // spawn_air with every drone at -1 and exclude = (ground == SKY) in [x, y] indexing (env.py:116-119)
@@ -630,12 +727,21 @@ __device__ __forceinline__ void env_reset(Group<T>& grp, const DevCfg& c, const 
     }
     noise_mantissas<T, NB>(tid, d, sk0, sk1, mant);
     int x = 0, y = 0;
-    extract_ranks<T, NB>(grp, tid, d, mant, candm, validm, n, [&](int j, int pos) {
-        if (drone_warp && lane == j) {
+    if constexpr (kWarp) {
+        extract_ranks<T, NB>(grp, tid, d, mant, candm, validm, n, [&](int j, int pos) {
+            if (lane == j) {
+                x = (int)d.divG((uint32_t)pos);
+                y = pos - x * G;
+            }
+        });
+    } else {
+        rank_positions<T, NB>(grp, d, sel, tid, mant, candm, validm, n);
+        if (drone_warp && lane < n) {
+            const int pos = sel.pos[lane];
             x = (int)d.divG((uint32_t)pos);
             y = pos - x * G;
         }
-    });
+    }
     // carrying = ground[air_y, air_x] == PACKET, then remove those packets (env.py:122-127)
     if (drone_warp) {
         int carry = 0;
