@@ -129,7 +129,7 @@ def cpu_rollout_rate(a, seconds, steps=None, warmup=1):
     p = E.Params(grid_size=a.grid, n_drones=a.drones, window_radius=a.radius, **factors(a))
     N = a.cpu_sample_envs
     cores = len(os.sched_getaffinity(0))
-    threads = min(cores, C.max_threads()) if C.max_threads() > 0 else cores
+    threads = cores       # explicit omp_set_num_threads in the oracle: torchrun's OMP_NUM_THREADS=1 default must not apply
     rng = np.random.default_rng(0)
     state = C.reset(C.split(np.array([0, 0], dtype=np.uint32), N), p, threads)
     acts = rng.integers(0, 5, size=(N, a.drones)).astype(np.int32)

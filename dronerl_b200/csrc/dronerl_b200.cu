@@ -251,6 +251,11 @@ struct drl_env {
     int8_t* s_actions;
     float* s_rewards;
     uint8_t* s_dones;
+    // drl_step_host pipeline: chunks of envs alternate between two side streams so the PCIe copies of one
+    // chunk overlap the kernel of another
+    cudaStream_t pipe_stream[2];
+    cudaEvent_t pipe_begin, pipe_end[2];
+    int per_sm_step;      // resident step CTAs per SM (grid sizing of chunk launches)
     char err[512];
 };
 
@@ -459,6 +464,7 @@ int drl_create(const drl_config* cfg, drl_env** out) {
         }
         const long long resident = (long long)per_sm * e->sm_count;
         *grids[i] = (int)(units < resident ? units : resident);
+        if (i == 0) e->per_sm_step = per_sm;
     }
     if (cudaMalloc(&e->d_stats, DRL_NUM_STATS * sizeof(unsigned long long)) != cudaSuccess ||
         cudaMemset(e->d_stats, 0, DRL_NUM_STATS * sizeof(unsigned long long)) != cudaSuccess) {
@@ -477,6 +483,11 @@ void drl_destroy(drl_env* env) {
     cudaFree(env->s_actions);
     cudaFree(env->s_rewards);
     cudaFree(env->s_dones);
+    for (int i = 0; i < 2; ++i) {
+        if (env->pipe_stream[i]) cudaStreamDestroy(env->pipe_stream[i]);
+        if (env->pipe_end[i]) cudaEventDestroy(env->pipe_end[i]);
+    }
+    if (env->pipe_begin) cudaEventDestroy(env->pipe_begin);
     delete env;
 }
 
@@ -581,26 +592,68 @@ static int ensure_scratch(drl_env* env) {
     CUDA_TRY(env, cudaMalloc(&env->s_actions, c.N * c.n));
     CUDA_TRY(env, cudaMalloc(&env->s_rewards, c.N * c.n * 4));
     CUDA_TRY(env, cudaMalloc(&env->s_dones, c.N * c.n));
+    for (int i = 0; i < 2; ++i) {
+        CUDA_TRY(env, cudaStreamCreateWithFlags(&env->pipe_stream[i], cudaStreamNonBlocking));
+        CUDA_TRY(env, cudaEventCreateWithFlags(&env->pipe_end[i], cudaEventDisableTiming));
+    }
+    CUDA_TRY(env, cudaEventCreateWithFlags(&env->pipe_begin, cudaEventDisableTiming));
     return DRL_OK;
+}
+
+// Step kernel over the env range [first, first + count) of the bound state (chunked launches).
+static int launch_step_range(drl_env* env, long long first, long long count, const uint32_t* d_keys, const int8_t* d_actions,
+                             float* d_rewards, uint8_t* d_dones, float* d_obs, cudaStream_t s) {
+    DevCfg dc = env->dc;
+    dc.N = count;
+    const long long n = dc.n;
+    const long long per_cta = env->warp_mode ? (long long)kWarpsPerBlock * env->envs_per_warp : 1;
+    const long long units = (count + per_cta - 1) / per_cta, resident = (long long)env->per_sm_step * env->sm_count;
+    const int threads = env->warp_mode ? kWarpsPerBlock * 32 : kCtaThreads;
+    float* obs = d_obs ? d_obs + first * n * dc.W2 * 6 : nullptr;
+    return launch(env, "step kernel", (const void*)pick_step(env), (int)(units < resident ? units : resident), threads,
+                  env->smem_bytes, (void*)s, dc, env->d_ground + first * dc.GS, env->d_drones + first * n, d_keys + 2 * first,
+                  d_actions + first * n, d_rewards + first * n, d_dones + first * n, obs, env->d_stats);
 }
 
 int drl_step_host(drl_env* env, const uint32_t key[2], const int8_t* h_actions, float* h_rewards, uint8_t* h_dones,
                   void* d_obs, float* h_obs, void* stream) {
     if (!env || !key || !h_actions || !h_rewards || !h_dones) return DRL_EINVAL;
+    if (!env->d_ground) return fail(env, DRL_ESTATE, "drl_step_host: state not bound (call drl_bind_state)%s");
     if (h_obs && !d_obs) return fail(env, DRL_EINVAL, "drl_step_host: h_obs needs a device obs buffer too%s");
+    if ((uintptr_t)d_obs & 7) return fail(env, DRL_EINVAL, "drl_step_host: obs must be 8-byte aligned%s");
     CUDA_TRY(env, cudaSetDevice(env->cfg.device));
     int rc = ensure_scratch(env);
     if (rc) return rc;
     const DevCfg& c = env->dc;
+    const long long n = c.n;
     cudaStream_t s = (cudaStream_t)stream;
-    CUDA_TRY(env, cudaMemcpyAsync(env->s_actions, h_actions, c.N * c.n, cudaMemcpyHostToDevice, s));
     rc = drl_split_keys(env, key, env->s_keys, stream);
     if (rc) return rc;
-    rc = drl_step(env, env->s_keys, env->s_actions, env->s_rewards, env->s_dones, d_obs, stream);
-    if (rc) return rc;
-    CUDA_TRY(env, cudaMemcpyAsync(h_rewards, env->s_rewards, c.N * c.n * 4, cudaMemcpyDeviceToHost, s));
-    CUDA_TRY(env, cudaMemcpyAsync(h_dones, env->s_dones, c.N * c.n, cudaMemcpyDeviceToHost, s));
-    if (h_obs) CUDA_TRY(env, cudaMemcpyAsync(h_obs, d_obs, c.N * c.n * (long long)c.W2 * 24, cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(env, cudaEventRecord(env->pipe_begin, s));
+    // chunks of a whole number of 1024-env blocks: H2D actions -> step+obs -> D2H rewards, dones (, obs)
+    const long long kMinChunk = 32768;
+    int chunks = (int)(c.N / kMinChunk);
+    chunks = chunks < 1 ? 1 : chunks > 8 ? 8 : chunks;
+    const long long per = ((c.N + chunks - 1) / chunks + 1023) / 1024 * 1024;
+    const long long obs_env = n * c.W2 * 6;     // floats per env
+    int used = 0;
+    for (long long first = 0; first < c.N; first += per, ++used) {
+        const long long count = c.N - first < per ? c.N - first : per;
+        cudaStream_t ps = env->pipe_stream[used & 1];
+        if (used < 2) CUDA_TRY(env, cudaStreamWaitEvent(ps, env->pipe_begin, 0));
+        CUDA_TRY(env, cudaMemcpyAsync(env->s_actions + first * n, h_actions + first * n, count * n, cudaMemcpyHostToDevice, ps));
+        rc = launch_step_range(env, first, count, env->s_keys, env->s_actions, env->s_rewards, env->s_dones, (float*)d_obs, ps);
+        if (rc) return rc;
+        CUDA_TRY(env, cudaMemcpyAsync(h_rewards + first * n, env->s_rewards + first * n, count * n * 4, cudaMemcpyDeviceToHost, ps));
+        CUDA_TRY(env, cudaMemcpyAsync(h_dones + first * n, env->s_dones + first * n, count * n, cudaMemcpyDeviceToHost, ps));
+        if (h_obs)
+            CUDA_TRY(env, cudaMemcpyAsync(h_obs + first * obs_env, (float*)d_obs + first * obs_env, count * obs_env * 4,
+                                          cudaMemcpyDeviceToHost, ps));
+    }
+    for (int i = 0; i < (used < 2 ? used : 2); ++i) {
+        CUDA_TRY(env, cudaEventRecord(env->pipe_end[i], env->pipe_stream[i]));
+        CUDA_TRY(env, cudaStreamWaitEvent(s, env->pipe_end[i], 0));
+    }
     CUDA_TRY(env, cudaStreamSynchronize(s));
     return DRL_OK;
 }

@@ -106,3 +106,36 @@ def test_sharded_slices_equal_unsharded(c_oracle):
     got_d = torch.cat([h.drones_raw for h in halves]).cpu().numpy()
     np.testing.assert_array_equal(got_g, full.ground_raw.cpu().numpy())
     np.testing.assert_array_equal(got_d, full.drones_raw.cpu().numpy())
+
+
+@pytest.mark.parametrize('N,G,n', [(70001, 9, 4), (300000, 8, 3), (999, 9, 4)])
+def test_step_host_pipeline_equals_device_step(N, G, n):
+    """drl_step_host (host buffers, chunked over two side streams) == drl_step on the same state/keys/actions."""
+    import ctypes
+    import dronerl_b200 as drl
+    from dronerl_b200 import _lib
+    from dronerl_b200.env import _vp, _stream
+    p = drl.DroneEnvParams(grid_size=G, n_drones=n)
+    env = drl.DeliveryDrones()
+    a = env.reset(drl.random.PRNGKey(1), p, num_envs=N)
+    b = a.clone()
+    W = p.window_size
+    for t in range(3):
+        acts = torch.from_numpy(np.random.default_rng(t).integers(0, 5, size=(N, n)).astype(np.int8))
+        key = drl.random.PRNGKey(50 + t)
+        a, rew, done, obs = env.step(key, a, acts.cuda(), p, return_obs=True)
+        h = env._state_handle(b, p)
+        h_act = acts.pin_memory()
+        h_rew = torch.empty((N, n), dtype=torch.float32).pin_memory()
+        h_done = torch.empty((N, n), dtype=torch.uint8).pin_memory()
+        d_obs = torch.empty((N, n, W, W, 6), dtype=torch.float32, device='cuda')
+        h_obs = torch.empty((N, n, W, W, 6), dtype=torch.float32).pin_memory() if N < 100000 else None
+        h.check(h.lib.drl_step_host(h.ptr, _lib.key_array(key), ctypes.c_void_p(h_act.data_ptr()),
+                                    ctypes.c_void_p(h_rew.data_ptr()), ctypes.c_void_p(h_done.data_ptr()), _vp(d_obs),
+                                    ctypes.c_void_p(h_obs.data_ptr() if h_obs is not None else 0), _stream()))
+        assert torch.equal(a.ground_raw, b.ground_raw) and torch.equal(a.drones_raw, b.drones_raw)
+        assert torch.equal(rew.cpu().view(torch.int32), h_rew.view(torch.int32))
+        assert torch.equal(done.cpu().view(torch.uint8), h_done)
+        assert torch.equal(obs.view(torch.int32), d_obs.view(torch.int32))
+        if h_obs is not None:
+            assert torch.equal(obs.cpu().view(torch.int32), h_obs.view(torch.int32))
