@@ -162,20 +162,53 @@ __device__ __forceinline__ Smem carve(unsigned char* base, const DevCfg& c) {
     return s;
 }
 
-// Cell owned by slot s of thread tid: threefry block b = tid + T*(s/2) yields the noise of
-// cells b (word 0) and b + H (word 1) -- jax's original random_bits layout.
-template <int T>
-__device__ __forceinline__ int slot_cell(int tid, int s, int H) { return tid + T * (s >> 1) + (s & 1) * H; }
+// Threefry block t of thread tid.  Warp mode interleaves blocks over the lanes; CTA mode gives each thread NB
+// CONSECUTIVE blocks so that its cells are two runs of NB bytes (scanned with 32-bit shared loads).
+template <int T, int NB>
+__device__ __forceinline__ int slot_block(int tid, int t) { return T == 32 ? tid + 32 * t : tid * NB + t; }
+
+// Cell owned by slot s of thread tid: block b = slot_block(s/2) yields the noise of cells b (word 0)
+// and b + H (word 1) -- jax's original random_bits layout.
+template <int T, int NB = 1>
+__device__ __forceinline__ int slot_cell(int tid, int s, int H) { return slot_block<T, NB>(tid, s >> 1) + (s & 1) * H; }
 
 template <int T, int NB, class D>
 __device__ __forceinline__ uint32_t valid_slots(int tid, const D& d) {
     uint32_t m = 0;
 #pragma unroll
     for (int s = 0; s < 2 * NB; ++s) {
-        const int b = tid + T * (s >> 1);
+        const int b = slot_block<T, NB>(tid, s >> 1);
         const int cell = b + (s & 1) * d.H();
         if (b < d.H() && cell < d.G2()) m |= 1u << s;
     }
+    return m;
+}
+
+// Mask of this thread's valid slots whose cell byte in ``arr`` satisfies ``pred``.
+template <int T, int NB, class D, class F>
+__device__ __forceinline__ uint32_t slot_mask(const uint8_t* arr, int tid, const D& d, uint32_t validm, F&& pred) {
+    uint32_t m = 0;
+    if constexpr (T != 32 && NB % 4 == 0) {
+        if ((d.H() & 3) == 0) {          // both runs are word aligned (arr is 16-byte aligned)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const uint32_t* w = reinterpret_cast<const uint32_t*>(arr + tid * NB + h * d.H());
+#pragma unroll
+                for (int q = 0; q < NB / 4; ++q) {
+                    // threads past the last block read shared memory beyond the grid (still inside the CTA's
+                    // allocation); validm discards those slots
+                    const uint32_t v = w[q];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        if (pred((v >> (8 * k)) & 0xFFu)) m |= 1u << (2 * (4 * q + k) + h);
+                }
+            }
+            return m & validm;
+        }
+    }
+#pragma unroll
+    for (int s = 0; s < 2 * NB; ++s)
+        if (((validm >> s) & 1u) && pred((uint32_t)arr[slot_cell<T, NB>(tid, s, d.H())])) m |= 1u << s;
     return m;
 }
 
@@ -184,7 +217,7 @@ template <int T, int NB, class D>
 __device__ __forceinline__ void noise_mantissas(int tid, const D& d, uint32_t k0, uint32_t k1, uint32_t (&mant)[2 * NB]) {
 #pragma unroll
     for (int t = 0; t < NB; ++t) {
-        const int b = tid + T * t;
+        const int b = slot_block<T, NB>(tid, t);
         uint32_t o0 = 0, o1 = 0;
         if (b < d.H()) {
             const int hi = d.H() + b;
@@ -218,7 +251,7 @@ __device__ __forceinline__ void extract_ranks(Group<T>& grp, int tid, const D& d
 #pragma unroll
         for (int s = 0; s < 2 * NB; ++s) {
             const uint32_t hi = ((candm >> s) & 1u) ? mant[s] + 1u : 0u;
-            key[s] = ((validm >> s) & 1u) ? ((hi << 8) | (uint32_t)(d.G2() - slot_cell<T>(tid, s, d.H()))) : 0u;
+            key[s] = ((validm >> s) & 1u) ? ((hi << 8) | (uint32_t)(d.G2() - slot_cell<T, NB>(tid, s, d.H()))) : 0u;
         }
         for (int j = 0; j < J_end; ++j) {
             uint32_t b = key[0];
@@ -238,7 +271,7 @@ __device__ __forceinline__ void extract_ranks(Group<T>& grp, int tid, const D& d
             for (int s = 0; s < 2 * NB; ++s) {
                 if ((live >> s) & 1u) {
                     const uint32_t hi = ((candm >> s) & 1u) ? mant[s] + 1u : 0u;
-                    const uint32_t lo = (uint32_t)(d.G2() - slot_cell<T>(tid, s, d.H()));
+                    const uint32_t lo = (uint32_t)(d.G2() - slot_cell<T, NB>(tid, s, d.H()));
                     if (hi > bh || (hi == bh && lo > bl)) { bh = hi; bl = lo; bs = s; }
                 }
             }
@@ -283,27 +316,40 @@ __device__ __forceinline__ void rank_positions(Group<T>& grp, const D& d, const 
                                                const uint32_t (&mant)[2 * NB], uint32_t candm, uint32_t validm, int J) {
     static_assert(T >= 256 && T % 32 == 0, "CTA mode");
     const int lane = tid & 31;
-    for (int i = tid; i < 256; i += T) sel.hist[i] = 0u;
-    if (tid == 0) sel.cnt[0] = 0u;
-    __syncthreads();
-#pragma unroll
-    for (int s = 0; s < 2 * NB; ++s)
-        if ((candm >> s) & 1u) atomicAdd(&sel.hist[mant[s] >> 15], 1u);
-    __syncthreads();
-    // every warp finds the threshold bin for itself (same histogram, same answer, no broadcast barrier)
-    uint32_t h[8];
+    // Only the top of the mantissa range can hold the J winners: histogram bins >= B0 first (about 8 J keys
+    // expected there when half the grid is a candidate), everything only if that was too few.
+    int B0;
     {
-        const uint4 a = reinterpret_cast<const uint4*>(sel.hist)[2 * lane], b = reinterpret_cast<const uint4*>(sel.hist)[2 * lane + 1];
-        h[0] = a.x; h[1] = a.y; h[2] = a.z; h[3] = a.w; h[4] = b.x; h[5] = b.y; h[6] = b.z; h[7] = b.w;
+        const int est = d.G2() >> 1;
+        const int top = (256 * 8 * J + est - 1) / (est > 0 ? est : 1);
+        B0 = top >= 256 ? 0 : 256 - top;
     }
-    const uint32_t local = h[0] + h[1] + h[2] + h[3] + h[4] + h[5] + h[6] + h[7];
-    uint32_t suf = local;                          // inclusive suffix sum over lanes
+    uint32_t h[8], local, suf, total;
+    while (true) {
+        for (int i = tid; i < 256; i += T) sel.hist[i] = 0u;
+        if (tid == 0) sel.cnt[0] = 0u;
+        __syncthreads();
 #pragma unroll
-    for (int off = 1; off < 32; off <<= 1) {
-        const uint32_t v = __shfl_down_sync(FULL, suf, off);
-        if (lane + off < 32) suf += v;
+        for (int s = 0; s < 2 * NB; ++s)
+            if (((candm >> s) & 1u) && (int)(mant[s] >> 15) >= B0) atomicAdd(&sel.hist[mant[s] >> 15], 1u);
+        __syncthreads();
+        // every warp finds the threshold bin for itself (same histogram, same answer, no broadcast barrier)
+        {
+            const uint4 a = reinterpret_cast<const uint4*>(sel.hist)[2 * lane], b = reinterpret_cast<const uint4*>(sel.hist)[2 * lane + 1];
+            h[0] = a.x; h[1] = a.y; h[2] = a.z; h[3] = a.w; h[4] = b.x; h[5] = b.y; h[6] = b.z; h[7] = b.w;
+        }
+        local = h[0] + h[1] + h[2] + h[3] + h[4] + h[5] + h[6] + h[7];
+        suf = local;                               // inclusive suffix sum over lanes
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint32_t v = __shfl_down_sync(FULL, suf, off);
+            if (lane + off < 32) suf += v;
+        }
+        total = __shfl_sync(FULL, suf, 0);
+        if (total >= (uint32_t)J || B0 == 0) break;
+        B0 = 0;
+        __syncthreads();                           // everyone has read the histogram before it is cleared again
     }
-    const uint32_t total = __shfl_sync(FULL, suf, 0);
     bool fast = total >= (uint32_t)J;
     int bstar = 0;
     uint32_t m = 0;
@@ -325,7 +371,7 @@ __device__ __forceinline__ void rank_positions(Group<T>& grp, const D& d, const 
         for (int s = 0; s < 2 * NB; ++s)
             if (((candm >> s) & 1u) && (int)(mant[s] >> 15) >= bstar) {
                 const uint32_t i = atomicAdd(sel.cnt, 1u);
-                sel.list[i] = ((unsigned long long)(mant[s] + 1u) << 16) | (unsigned)(d.G2() - slot_cell<T>(tid, s, d.H()));
+                sel.list[i] = ((unsigned long long)(mant[s] + 1u) << 16) | (unsigned)(d.G2() - slot_cell<T, NB>(tid, s, d.H()));
             }
         __syncthreads();
         for (int t = tid; t < (int)m; t += T) {
@@ -532,9 +578,7 @@ __device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const D
     bool have_oldsky = false;
     auto capture_oldsky = [&]() {
         if (!have_oldsky) {
-#pragma unroll
-            for (int s = 0; s < 2 * NB; ++s)
-                if (((validm >> s) & 1u) && sm.sg[slot_cell<T>(tid, s, d.H())] == SKY) oldsky |= 1u << s;
+            oldsky = slot_mask<T, NB>(sm.sg, tid, d, validm, [](uint32_t v) { return v == (uint32_t)SKY; });
             have_oldsky = true;
         }
     };
@@ -610,12 +654,8 @@ __device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const D
     const int F1 = F0 + npick;
     uint32_t freem = 0;
     auto scan_free = [&]() {
-        int fc = 0;
-        freem = 0;
-#pragma unroll
-        for (int s = 0; s < 2 * NB; ++s)
-            if (((validm >> s) & 1u) && sm.sg[slot_cell<T>(tid, s, d.H())] == 0) { freem |= 1u << s; ++fc; }
-        return fc;
+        freem = slot_mask<T, NB>(sm.sg, tid, d, validm, [](uint32_t v) { return v == 0u; });
+        return __popc(freem);
     };
 
     bool have_split = false, have_noise = false;
@@ -659,12 +699,10 @@ __device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const D
         if (drone_warp && surv) sm.code[x * G + y] = 1;
         Group<T>::sync();                                   // also orders the ground writes above
         capture_oldsky();
-        uint32_t candm = 0;
+        uint32_t candm = slot_mask<T, NB>(sm.code, tid, d, validm, [](uint32_t v) { return v == 0u; }) & ~oldsky;
 #pragma unroll
-        for (int s = 0; s < 2 * NB; ++s) {
-            const int cell = slot_cell<T>(tid, s, d.H());
-            if (((validm >> s) & 1u) && !((oldsky >> s) & 1u) && cell != G2 - 1 && sm.code[cell] == 0) candm |= 1u << s;
-        }
+        for (int s = 0; s < 2 * NB; ++s)
+            if (slot_cell<T, NB>(tid, s, d.H()) == G2 - 1) candm &= ~(1u << s);
         noise_mantissas<T, NB>(tid, d, sk0, sk1, mant);
         rank_positions<T, NB>(grp, d, sel, tid, mant, candm, validm, 32 - __clz(mDone));
         if (drone_warp && surv) sm.code[x * G + y] = 0;     // restore the all-zero invariant
@@ -701,10 +739,7 @@ __device__ __forceinline__ void env_reset(Group<T>& grp, const DevCfg& c, const 
 #pragma unroll 1
     for (int t = 0; t < 4; ++t) {
         split_warp(k0, k1, sk0, sk1);
-        uint32_t freem = 0;
-#pragma unroll
-        for (int s = 0; s < 2 * NB; ++s)
-            if (((validm >> s) & 1u) && sm.sg[slot_cell<T>(tid, s, d.H())] == 0) freem |= 1u << s;
+        const uint32_t freem = slot_mask<T, NB>(sm.sg, tid, d, validm, [](uint32_t v) { return v == 0u; });
         noise_mantissas<T, NB>(tid, d, sk0, sk1, mant);
         const int obj = objs[t];
         if constexpr (kWarp) {
@@ -719,12 +754,10 @@ __device__ __forceinline__ void env_reset(Group<T>& grp, const DevCfg& c, const 
     }
     // spawn_air with every drone at -1 and exclude = (ground == SKY) in [x, y] indexing (env.py:116-119)
     split_warp(k0, k1, sk0, sk1);
-    uint32_t candm = 0;
+    uint32_t candm = slot_mask<T, NB>(sm.sg, tid, d, validm, [](uint32_t v) { return v != (uint32_t)SKY; });
 #pragma unroll
-    for (int s = 0; s < 2 * NB; ++s) {
-        const int cell = slot_cell<T>(tid, s, d.H());
-        if (((validm >> s) & 1u) && cell != G2 - 1 && sm.sg[cell] != SKY) candm |= 1u << s;
-    }
+    for (int s = 0; s < 2 * NB; ++s)
+        if (slot_cell<T, NB>(tid, s, d.H()) == G2 - 1) candm &= ~(1u << s);
     noise_mantissas<T, NB>(tid, d, sk0, sk1, mant);
     int x = 0, y = 0;
     if constexpr (kWarp) {
