@@ -107,7 +107,7 @@ k_obs_warp(const __grid_constant__ DevCfg c, const uint8_t* __restrict__ ground,
 // ---- CTA-per-env kernels (larger grids) -------------------------------------------------------
 
 template <int NB, class D>
-__global__ void __launch_bounds__(kCtaThreads)
+__global__ void __launch_bounds__(kCtaThreads, 3)
 k_step_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint32_t* __restrict__ drones,
            const uint32_t* __restrict__ keys, const int8_t* __restrict__ actions, float* __restrict__ rewards,
            uint8_t* __restrict__ dones, float* __restrict__ obs, unsigned long long* __restrict__ stats) {
@@ -417,7 +417,7 @@ int drl_create(const drl_config* cfg, drl_env** out) {
     c.tile_bufs = 1;
     e->envs_per_warp = !e->warp_mode ? 1 : n <= 8 ? 4 : n <= 16 ? 2 : 1;
     const int Q = e->envs_per_warp;
-    c.off_code = 2 * Q * c.GS;                      // two staging buffers of Q ground rows (warp step kernel)
+    c.off_code = (e->warp_mode ? 2 : 1) * Q * c.GS;  // warp step kernel: two staging buffers of Q ground rows
     c.off_sdr = c.off_code + Q * round_up((int)G2, 16);
     c.off_sdf = c.off_sdr + 128;
     c.off_misc = c.off_sdf + 128;
