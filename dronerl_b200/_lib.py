@@ -38,6 +38,10 @@ SYMBOLS = {
     'drl_bind_state': (ctypes.c_int, [_vp, _vp, _vp]),
     'drl_split_keys': (ctypes.c_int, [_vp, c_u32p, _vp, _vp]),
     'drl_randint_actions': (ctypes.c_int, [_vp, c_u32p, _i32, _vp, _vp]),
+    'drl_key_split_dev': (ctypes.c_int, [_vp, _i32, _vp, _vp]),
+    'drl_split_keys_dev': (ctypes.c_int, [_vp, _vp, _vp, _vp]),
+    'drl_randint_actions_dev': (ctypes.c_int, [_vp, _vp, _i32, _vp, _vp]),
+    'drl_set_obs_drones': (ctypes.c_int, [_vp, _i32]),
     'drl_reset': (ctypes.c_int, [_vp, _vp, _vp]),
     'drl_step': (ctypes.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     'drl_get_obs': (ctypes.c_int, [_vp, _vp, _vp]),

@@ -42,7 +42,7 @@ __device__ __forceinline__ void zero_code(const DevCfg& c, const Smem& sm, int t
 // ---- warp-per-env kernels (grids up to 128 cells) ---------------------------------------------
 
 template <int NB, int Q, class D>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32, 3)
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, DRL_STEP_MIN_BLOCKS)
 k_step_warp(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint32_t* __restrict__ drones,
             const uint32_t* __restrict__ keys, const int8_t* __restrict__ actions, float* __restrict__ rewards,
             uint8_t* __restrict__ dones, float* __restrict__ obs, unsigned long long* __restrict__ stats) {
@@ -212,22 +212,35 @@ k_obs_cta(const __grid_constant__ DevCfg c, const uint8_t* __restrict__ ground, 
 // ---- key / action derivation --------------------------------------------------------------------
 
 // keys_out[e] = split(key, Ng)[off + e]: flat words 2(off+e), 2(off+e)+1 of random_bits(key, 2 Ng)
-__global__ void k_split_keys(uint32_t k0, uint32_t k1, long long Ng, long long off, long long Nl,
-                             uint32_t* __restrict__ out) {
+// (the parent key comes by value, or from device memory when ``dkey`` is set: CUDA-graph friendly)
+__global__ void k_split_keys(uint32_t k0, uint32_t k1, const uint32_t* __restrict__ dkey, long long Ng, long long off,
+                             long long Nl, uint32_t* __restrict__ out) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;   // local flat word
     if (i >= 2 * Nl) return;
+    if (dkey != nullptr) { k0 = dkey[0]; k1 = dkey[1]; }
     out[i] = drl_random_bits_at(k0, k1, (uint64_t)(2 * Ng), (uint64_t)(2 * off + i));
 }
 
 // actions_out = int8(randint(key, (Ng, n), 0, maxval))[off : off + Nl]; (a0,a1),(b0,b1) = split(key)
-__global__ void k_randint(uint32_t a0, uint32_t a1, uint32_t b0, uint32_t b1, long long total, long long first,
-                          long long count, uint32_t span, uint32_t mult, int8_t* __restrict__ out) {
+__global__ void k_randint(uint32_t a0, uint32_t a1, uint32_t b0, uint32_t b1, const uint32_t* __restrict__ dkeys,
+                          long long total, long long first, long long count, uint32_t span, uint32_t mult,
+                          int8_t* __restrict__ out) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= count) return;
+    if (dkeys != nullptr) { a0 = dkeys[0]; a1 = dkeys[1]; b0 = dkeys[2]; b1 = dkeys[3]; }
     const uint32_t hi = drl_random_bits_at(a0, a1, (uint64_t)total, (uint64_t)(first + i));
     const uint32_t lo = drl_random_bits_at(b0, b1, (uint64_t)total, (uint64_t)(first + i));
     const uint32_t v = ((hi % span) * mult + (lo % span)) % span;
     out[i] = (int8_t)v;
+}
+
+// out[i] = split(key, num)[i] with the key read from device memory; one block, in-place safe (``out`` may
+// start at ``dkey``): every thread reads the key before anyone writes
+__global__ void k_key_split_dev(const uint32_t* dkey, int num, uint32_t* out) {
+    const uint32_t k0 = dkey[0], k1 = dkey[1];
+    __syncthreads();
+    const int i = threadIdx.x;
+    if (i < 2 * num) out[i] = drl_random_bits_at(k0, k1, (uint64_t)(2 * num), (uint64_t)i);
 }
 
 // =================================================================================================
@@ -256,6 +269,7 @@ struct drl_env {
     cudaStream_t pipe_stream[2];
     cudaEvent_t pipe_begin, pipe_end[2];
     int per_sm_step;      // resident step CTAs per SM (grid sizing of chunk launches)
+    int smem_optin;       // device limit of opt-in dynamic shared memory per CTA
     char err[512];
 };
 
@@ -286,6 +300,7 @@ using D833 = Dims<8, 3, 3>;    // DroneEnvParams dataclass defaults (jax_impl/en
 
 static int static_shape(const drl_env* e) {
     const DevCfg& c = e->dc;
+    if (c.obs_n != c.n) return 0;      // reduced-obs mode runs the dynamic-shape instances
     if (c.G == 9 && c.n == 4 && c.r == 3) return 1;
     if (c.G == 8 && c.n == 3 && c.r == 3) return 2;
     return 0;
@@ -333,6 +348,31 @@ static int launch(drl_env* env, const char* what, const void* fn, int grid, int 
     if (ce != cudaSuccess) {
         (void)cudaGetLastError();
         return fail(env, DRL_ECUDA, "launch of %s failed: CUDA error %lld", what, (long long)ce);
+    }
+    return DRL_OK;
+}
+
+// Shared-memory opt-in, occupancy and persistent grid sizes of the three kernels this handle launches.
+static int configure_launches(drl_env* e) {
+    const DevCfg& c = e->dc;
+    const int Q = e->envs_per_warp;
+    const int threads = e->warp_mode ? kWarpsPerBlock * 32 : kCtaThreads;
+    const void* fns[3] = {(const void*)pick_step(e), (const void*)pick_reset(e), (const void*)pick_obs(e)};
+    int* grids[3] = {&e->grid_step, &e->grid_reset, &e->grid_obs};
+    for (int i = 0; i < 3; ++i) {
+        const long long per_cta = e->warp_mode ? (long long)kWarpsPerBlock * (i == 0 ? Q : 1) : 1;
+        const long long units = (c.N + per_cta - 1) / per_cta;
+        // the attribute belongs to the FUNCTION, which handles of other shapes share: always grant the device's
+        // opt-in maximum (a smaller value set by a later handle would make this handle's launches invalid)
+        cudaError_t ce = cudaFuncSetAttribute(fns[i], cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem_optin);
+        int per_sm = 0;
+        if (ce == cudaSuccess) ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fns[i], threads, e->smem_bytes);
+        if (ce != cudaSuccess || per_sm < 1)
+            return fail(e, DRL_ECUDA, "kernel %s setup failed (CUDA error %lld, blocks/SM %lld)",
+                        i == 0 ? "step" : i == 1 ? "reset" : "obs", (long long)ce, (long long)per_sm);
+        const long long resident = (long long)per_sm * e->sm_count;
+        *grids[i] = (int)(units < resident ? units : resident);
+        if (i == 0) e->per_sm_step = per_sm;
     }
     return DRL_OK;
 }
@@ -412,6 +452,7 @@ int drl_create(const drl_config* cfg, drl_env** out) {
     const int cell_bytes = c.W2 * 24;
     e->nb = e->warp_mode ? (c.H <= 32 ? 1 : 2) : (c.H <= 2 * kCtaThreads ? 2 : c.H <= 8 * kCtaThreads ? 8 : 16);
     c.tile_drones = tile_drones_for(n, c.W2, e->warp_mode);
+    c.obs_n = n;
     c.ntiles = (n + c.tile_drones - 1) / c.tile_drones;
     c.tile_stride = round_up(c.tile_drones * cell_bytes, 128);
     c.tile_bufs = 1;
@@ -445,28 +486,14 @@ int drl_create(const drl_config* cfg, drl_env** out) {
                     need, (long long)prop.sharedMemPerBlockOptin);
     }
 
-    const int threads = e->warp_mode ? kWarpsPerBlock * 32 : kCtaThreads;
-    const void* fns[3] = {(const void*)pick_step(e), (const void*)pick_reset(e), (const void*)pick_obs(e)};
-    int* grids[3] = {&e->grid_step, &e->grid_reset, &e->grid_obs};
-    for (int i = 0; i < 3; ++i) {
-        const long long per_cta = e->warp_mode ? (long long)kWarpsPerBlock * (i == 0 ? Q : 1) : 1;
-        const long long units = (c.N + per_cta - 1) / per_cta;
-        // the attribute belongs to the FUNCTION, which handles of other shapes share: always grant the device's
-        // opt-in maximum (a smaller value set by a later handle would make this handle's launches invalid)
-        cudaError_t ce = cudaFuncSetAttribute(fns[i], cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                              (int)prop.sharedMemPerBlockOptin);
-        int per_sm = 0;
-        if (ce == cudaSuccess) ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fns[i], threads, e->smem_bytes);
-        if (ce != cudaSuccess || per_sm < 1) {
-            delete e;
-            return fail(nullptr, DRL_ECUDA, "kernel %s setup failed (CUDA error %lld, blocks/SM %lld)", i == 0 ? "step" : i == 1 ? "reset" : "obs",
-                        (long long)ce, (long long)per_sm);
-        }
-        const long long resident = (long long)per_sm * e->sm_count;
-        *grids[i] = (int)(units < resident ? units : resident);
-        if (i == 0) e->per_sm_step = per_sm;
+    e->smem_optin = (int)prop.sharedMemPerBlockOptin;
+    if (configure_launches(e) != DRL_OK) {
+        snprintf(g_create_err, sizeof(g_create_err), "%s", e->err);
+        delete e;
+        return DRL_ECUDA;
     }
-    if (cudaMalloc(&e->d_stats, DRL_NUM_STATS * sizeof(unsigned long long)) != cudaSuccess ||
+    // statistics block + 16 bytes of key scratch for the *_dev entry points
+    if (cudaMalloc(&e->d_stats, (DRL_NUM_STATS + 2) * sizeof(unsigned long long)) != cudaSuccess ||
         cudaMemset(e->d_stats, 0, DRL_NUM_STATS * sizeof(unsigned long long)) != cudaSuccess) {
         delete e;
         return fail(nullptr, DRL_ECUDA, "cudaMalloc of the statistics block failed%s");
@@ -501,9 +528,17 @@ int drl_get_layout(const drl_env* env, drl_layout* out) {
     out->actions_bytes = c.N * c.n;
     out->rewards_bytes = c.N * c.n * 4;
     out->dones_bytes = c.N * c.n;
-    out->obs_bytes = c.N * c.n * (long long)c.W2 * 24;
+    out->obs_bytes = c.N * c.obs_n * (long long)c.W2 * 24;
     out->algorithmic_bytes_per_env_step = 24ll * c.n * c.W2 + 2ll * c.G2 + 14ll * c.n;
     return DRL_OK;
+}
+
+int drl_set_obs_drones(drl_env* env, int32_t k) {
+    if (!env) return DRL_EINVAL;
+    if (k < 1 || k > env->dc.n) return fail(env, DRL_EINVAL, "drl_set_obs_drones: need 1 <= k <= n_drones%s");
+    env->dc.obs_n = k;
+    env->dc.ntiles = (k + env->dc.tile_drones - 1) / env->dc.tile_drones;
+    return configure_launches(env);     // the kernel instances may have changed (static <-> dynamic shape)
 }
 
 int drl_bind_state(drl_env* env, void* d_ground, void* d_drones) {
@@ -520,7 +555,7 @@ int drl_split_n(const uint32_t key[2], int64_t num, int64_t offset, int64_t coun
     if (!key || !d_out || num < 1 || offset < 0 || count < 0 || offset + count > num || num > (1ll << 30)) return DRL_EINVAL;
     if (count == 0) return DRL_OK;
     return launch(nullptr, "split kernel", (const void*)k_split_keys, (int)((2 * count + 255) / 256), 256, 0, stream, key[0],
-                  key[1], (long long)num, (long long)offset, (long long)count, (uint32_t*)d_out);
+                  key[1], (const uint32_t*)nullptr, (long long)num, (long long)offset, (long long)count, (uint32_t*)d_out);
 }
 
 int drl_randint_n(const uint32_t key[2], int64_t total, int64_t first, int64_t count, int32_t maxval, void* d_out,
@@ -535,7 +570,39 @@ int drl_randint_n(const uint32_t key[2], int64_t total, int64_t first, int64_t c
     uint32_t mult = 65536u % span;
     mult = (mult * mult) % span;
     return launch(nullptr, "randint kernel", (const void*)k_randint, (int)((count + 255) / 256), 256, 0, stream, k1[0], k1[1],
-                  k2[0], k2[1], (long long)total, (long long)first, (long long)count, span, mult, (int8_t*)d_out);
+                  k2[0], k2[1], (const uint32_t*)nullptr, (long long)total, (long long)first, (long long)count, span, mult,
+                  (int8_t*)d_out);
+}
+
+int drl_key_split_dev(const void* d_key, int32_t num, void* d_out, void* stream) {
+    if (!d_key || !d_out || num < 1 || num > 512) return DRL_EINVAL;
+    return launch(nullptr, "key split kernel", (const void*)k_key_split_dev, 1, 2 * num <= 32 ? 32 : (2 * num + 31) / 32 * 32, 0,
+                  stream, (const uint32_t*)d_key, (int)num, (uint32_t*)d_out);
+}
+
+int drl_split_keys_dev(drl_env* env, const void* d_key, void* d_keys_out, void* stream) {
+    if (!env || !d_key || !d_keys_out) return DRL_EINVAL;
+    CUDA_TRY(env, cudaSetDevice(env->cfg.device));
+    return launch(env, "split kernel", (const void*)k_split_keys, (int)((2 * env->dc.N + 255) / 256), 256, 0, stream, 0u, 0u,
+                  (const uint32_t*)d_key, (long long)env->cfg.num_envs_global, (long long)env->cfg.env_offset,
+                  (long long)env->dc.N, (uint32_t*)d_keys_out);
+}
+
+int drl_randint_actions_dev(drl_env* env, const void* d_key, int32_t maxval, void* d_actions_out, void* stream) {
+    if (!env || !d_key || !d_actions_out) return DRL_EINVAL;
+    if (maxval < 1 || maxval > 127) return fail(env, DRL_EINVAL, "drl_randint_actions_dev: maxval must be in 1..127%s");
+    const long long n = env->dc.n, total = env->cfg.num_envs_global * n;
+    if (total >= (1ll << 32)) return fail(env, DRL_EINVAL, "drl_randint_actions_dev: too many actions (>= 2^32)%s");
+    CUDA_TRY(env, cudaSetDevice(env->cfg.device));
+    uint32_t* k12 = (uint32_t*)(env->d_stats + DRL_NUM_STATS);        // 4 words of handle-owned scratch
+    int rc = drl_key_split_dev(d_key, 2, k12, stream);               // _randint: k1, k2 = split(key)
+    if (rc) return fail(env, rc, "drl_randint_actions_dev: key split launch failed%s");
+    const uint32_t span = (uint32_t)maxval;
+    uint32_t mult = 65536u % span;
+    mult = (mult * mult) % span;
+    return launch(env, "randint kernel", (const void*)k_randint, (int)((env->dc.N * n + 255) / 256), 256, 0, stream, 0u, 0u, 0u, 0u,
+                  (const uint32_t*)k12, total, (long long)(env->cfg.env_offset * n), (long long)(env->dc.N * n), span, mult,
+                  (int8_t*)d_actions_out);
 }
 
 int drl_split_keys(drl_env* env, const uint32_t key[2], void* d_keys_out, void* stream) {
@@ -609,7 +676,7 @@ static int launch_step_range(drl_env* env, long long first, long long count, con
     const long long per_cta = env->warp_mode ? (long long)kWarpsPerBlock * env->envs_per_warp : 1;
     const long long units = (count + per_cta - 1) / per_cta, resident = (long long)env->per_sm_step * env->sm_count;
     const int threads = env->warp_mode ? kWarpsPerBlock * 32 : kCtaThreads;
-    float* obs = d_obs ? d_obs + first * n * dc.W2 * 6 : nullptr;
+    float* obs = d_obs ? d_obs + first * dc.obs_n * dc.W2 * 6 : nullptr;
     return launch(env, "step kernel", (const void*)pick_step(env), (int)(units < resident ? units : resident), threads,
                   env->smem_bytes, (void*)s, dc, env->d_ground + first * dc.GS, env->d_drones + first * n, d_keys + 2 * first,
                   d_actions + first * n, d_rewards + first * n, d_dones + first * n, obs, env->d_stats);
@@ -635,7 +702,7 @@ int drl_step_host(drl_env* env, const uint32_t key[2], const int8_t* h_actions, 
     int chunks = (int)(c.N / kMinChunk);
     chunks = chunks < 1 ? 1 : chunks > 8 ? 8 : chunks;
     const long long per = ((c.N + chunks - 1) / chunks + 1023) / 1024 * 1024;
-    const long long obs_env = n * c.W2 * 6;     // floats per env
+    const long long obs_env = (long long)c.obs_n * c.W2 * 6;     // floats per env
     int used = 0;
     for (long long first = 0; first < c.N; first += per, ++used) {
         const long long count = c.N - first < per ? c.N - first : per;

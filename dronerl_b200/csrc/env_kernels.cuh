@@ -29,7 +29,13 @@ constexpr unsigned FULL = 0xFFFFFFFFu;
 enum : int { SKY = 2, STATION = 3, DROPZONE = 4, PACKET = 5 };
 enum : int { A_LEFT = 0, A_DOWN = 1, A_RIGHT = 2, A_UP = 3 };
 constexpr int kCtaThreads = 256;
-constexpr int kWarpsPerBlock = 8;
+#ifndef DRL_WARPS_PER_BLOCK
+#define DRL_WARPS_PER_BLOCK 8
+#endif
+#ifndef DRL_STEP_MIN_BLOCKS
+#define DRL_STEP_MIN_BLOCKS 3
+#endif
+constexpr int kWarpsPerBlock = DRL_WARPS_PER_BLOCK;   // warp mode: envs groups stepped per CTA
 
 struct DevCfg {
     int G, G2, H, GS;          // grid side, cells, ceil(cells/2) (threefry blocks per noise vector), ground row stride
@@ -40,6 +46,7 @@ struct DevCfg {
     float rw_pickup, rw_delivery, rw_crash, rw_charge;
     uint32_t mulG, mulW, mulW2, mulN;  // magic multipliers: x / d == umulhi(x, mul) for x*d < 2^32
     int tile_drones, ntiles;   // drones per obs tile, tiles per env
+    int obs_n;                 // drones whose windows are rendered (the first obs_n; n by default)
     int tile_stride;           // bytes reserved per obs tile buffer
     int tile_bufs;             // tile buffers per warp (1, or 2 alternating)
     // shared-memory carve-up (bytes from the group's base)
@@ -84,6 +91,7 @@ struct Dims {
     __device__ __forceinline__ int W() const { return kStatic ? kW : c.W; }
     __device__ __forceinline__ int W2() const { return kStatic ? kW * kW : c.W2; }
     __device__ __forceinline__ int center() const { return kStatic ? R_ * kW + R_ : c.center; }
+    __device__ __forceinline__ int obs_n() const { return kStatic ? N_ : c.obs_n; }
     __device__ __forceinline__ int tile_drones() const { return kStatic ? kTD : c.tile_drones; }
     __device__ __forceinline__ int ntiles() const { return kStatic ? (N_ + (kTD ? kTD : 1) - 1) / (kTD ? kTD : 1) : c.ntiles; }
     __device__ __forceinline__ uint32_t divG(uint32_t x) const {
@@ -546,11 +554,11 @@ __device__ __forceinline__ void obs_tiles(const D& d, const DevCfg& c, const Sme
                                           int& tsel, int first, int step, int lane) {
     for (int t = first; t < d.ntiles(); t += step) {
         const int d0 = t * d.tile_drones();
-        const int d1 = min(d.n(), d0 + d.tile_drones());
+        const int d1 = min(d.obs_n(), d0 + d.tile_drones());
         float* buf = tile + tsel * (c.tile_stride >> 2);
         tsel ^= (c.tile_bufs - 1);
         compose_tile(d, sm, d0, d1, buf, lane, c.tile_bufs);
-        float* gdst = obs + ((size_t)e * d.n() + d0) * (size_t)(d.W2() * 6);
+        float* gdst = obs + ((size_t)e * d.obs_n() + d0) * (size_t)(d.W2() * 6);
         tile_store(gdst, buf, (d1 - d0) * d.W2() * 24, lane);
     }
 }

@@ -37,7 +37,7 @@ def _vp(t):
 class _Handle:
     """One drl_env per (params, slice, device)."""
 
-    def __init__(self, params, num_envs, env_offset, num_envs_global, device_index):
+    def __init__(self, params, num_envs, env_offset, num_envs_global, device_index, obs_drones=None):
         self.lib = _lib.load()
         cfg = _lib.Config(
             params.grid_size, params.n_drones, params.window_radius, params.packets_factor,
@@ -52,6 +52,10 @@ class _Handle:
                 raise ValueError(msg)          # the reference's reset-time ValueError (env.py:96-104)
             raise RuntimeError(f'drl_create failed ({rc}): {msg}')
         self.ptr = ptr
+        if obs_drones is not None and obs_drones != params.n_drones:
+            rc = self.lib.drl_set_obs_drones(ptr, int(obs_drones))
+            if rc != 0:
+                raise ValueError(self.lib.drl_last_error(ptr).decode())
         self.layout = _lib.Layout()
         self.lib.drl_get_layout(self.ptr, ctypes.byref(self.layout))
 
@@ -103,18 +107,19 @@ class DeliveryDrones:
             raise RuntimeError('dronerl_b200 needs a CUDA (sm_100) device; there is no CPU fallback')
         return torch.device('cuda', torch.cuda.current_device())
 
-    def _handle(self, params, num_envs, env_offset, num_envs_global, device):
+    def _handle(self, params, num_envs, env_offset, num_envs_global, device, obs_drones=None):
         if params.wrapper != 'window':
             raise NotImplementedError     # env.py:275-277
         idx = device.index if device.index is not None else torch.cuda.current_device()
-        k = (params, num_envs, env_offset, num_envs_global, idx)
+        obs_drones = params.n_drones if obs_drones is None else int(obs_drones)
+        k = (params, num_envs, env_offset, num_envs_global, idx, obs_drones)
         h = self._handles.get(k)
         if h is None:
-            h = self._handles[k] = _Handle(params, num_envs, env_offset, num_envs_global, idx)
+            h = self._handles[k] = _Handle(params, num_envs, env_offset, num_envs_global, idx, obs_drones)
         return h
 
-    def _state_handle(self, state, params):
-        h = self._handle(params, state.num_envs, state.env_offset, state.num_envs_global, state.device)
+    def _state_handle(self, state, params, obs_drones=None):
+        h = self._handle(params, state.num_envs, state.env_offset, state.num_envs_global, state.device, obs_drones)
         h.check(h.lib.drl_bind_state(h.ptr, _vp(state.ground_raw), _vp(state.drones_raw)))
         return h
 
@@ -157,16 +162,17 @@ class DeliveryDrones:
             h.check(h.lib.drl_reset(h.ptr, _vp(keys), _stream()))
         return state
 
-    def step(self, key, state: DroneEnvState, actions, params: DroneEnvParams, return_obs=False):
+    def step(self, key, state: DroneEnvState, actions, params: DroneEnvParams, return_obs=False, obs_drones=None):
         """``env.step(key, state, actions, params)`` / its vmap -- env.py:137-250.
 
         Returns ``(state, rewards float32, dones bool)``; with ``return_obs=True`` the observation of
-        the new state (``get_obs``, env.py:274-309) is produced by the same kernel and appended.
+        the new state (``get_obs``, env.py:274-309) is produced by the same kernel and appended;
+        ``obs_drones=k`` renders only the first k drones' windows (``obs[:, :k]``, train_jax.py:56).
         """
         device = state.device
         N, n = state.num_envs, params.n_drones
         with torch.cuda.device(device):
-            h = self._state_handle(state, params)
+            h = self._state_handle(state, params, obs_drones if return_obs else None)
             if not state.batched:
                 keys = torch.from_numpy(_host_key(key).reshape(1, 2).copy()).to(device)
             else:
@@ -176,7 +182,7 @@ class DeliveryDrones:
             acts = actions.to(device=device, dtype=torch.int8).reshape(N, n).contiguous()
             rewards = torch.empty((N, n), dtype=torch.float32, device=device)
             dones = torch.empty((N, n), dtype=torch.uint8, device=device)
-            obs = self._obs_buffer(state, params) if return_obs else None
+            obs = self._obs_buffer(state, params, obs_drones) if return_obs else None
             h.check(h.lib.drl_step(h.ptr, _vp(keys), _vp(acts), _vp(rewards), _vp(dones), _vp(obs), _stream()))
         dones = dones.view(torch.bool)
         if not state.batched:
@@ -184,17 +190,19 @@ class DeliveryDrones:
             obs = obs[0] if obs is not None else None
         return (state, rewards, dones, obs) if return_obs else (state, rewards, dones)
 
-    def _obs_buffer(self, state, params):
+    def _obs_buffer(self, state, params, obs_drones=None):
         W = params.window_size
-        return torch.empty((state.num_envs, params.n_drones, W, W, 6), dtype=torch.float32, device=state.device)
+        k = params.n_drones if obs_drones is None else int(obs_drones)
+        return torch.empty((state.num_envs, k, W, W, 6), dtype=torch.float32, device=state.device)
 
-    def get_obs(self, state: DroneEnvState, params: DroneEnvParams, out=None):
-        """``env.get_obs(state, params)`` / its vmap -- env.py:274-309: float32 ``[..., n, W, W, 6]``."""
+    def get_obs(self, state: DroneEnvState, params: DroneEnvParams, out=None, obs_drones=None):
+        """``env.get_obs(state, params)`` / its vmap -- env.py:274-309: float32 ``[..., n, W, W, 6]``
+        (``[..., k, W, W, 6]`` with ``obs_drones=k``)."""
         if params.wrapper != 'window':
             raise NotImplementedError
         with torch.cuda.device(state.device):
-            h = self._state_handle(state, params)
-            obs = self._obs_buffer(state, params) if out is None else out
+            h = self._state_handle(state, params, obs_drones)
+            obs = self._obs_buffer(state, params, obs_drones) if out is None else out
             h.check(h.lib.drl_get_obs(h.ptr, _vp(obs), _stream()))
         return obs if state.batched else obs[0]
 

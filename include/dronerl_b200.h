@@ -124,6 +124,20 @@ int drl_split_keys(drl_env* env, const uint32_t key[2], void* d_keys_out, void* 
  * (train_jax.py:44; jax_impl/agents/rand.py:13). */
 int drl_randint_actions(drl_env* env, const uint32_t key[2], int32_t maxval, void* d_actions_out, void* stream);
 
+/* Device-resident key chain, so that a whole trainer step can be captured in a CUDA graph (a key passed by
+ * value would be frozen into the graph): d_out[i] = jax.random.split(key, num)[i], i < num <= 512, with the
+ * key READ FROM DEVICE MEMORY at d_key.  In-place use is allowed (d_out == d_key): ``rng, k = split(rng)`` of
+ * train_jax.py:43,52,82 is drl_key_split_dev(d_rng, 2, d_rng) on a 4-word buffer {rng, k}. */
+int drl_key_split_dev(const void* d_key, int32_t num, void* d_out, void* stream);
+/* drl_split_keys / drl_randint_actions with the parent key read from device memory. */
+int drl_split_keys_dev(drl_env* env, const void* d_key, void* d_keys_out, void* stream);
+int drl_randint_actions_dev(drl_env* env, const void* d_key, int32_t maxval, void* d_actions_out, void* stream);
+
+/* Reduced-observation mode: render only the first k drones' windows (obs becomes [num_envs][k][W][W][6]).
+ * The reference trainer keeps drone 0's window only (train_jax.py:56,193: ``next_obs[:, :1]``); k = n_drones
+ * (the default) is the reference's full get_obs. */
+int drl_set_obs_drones(drl_env* env, int32_t k);
+
 /* vmap(env.reset)(keys, params)  -- jax_impl/env/env.py:89-135 (train_jax.py:103,189). */
 int drl_reset(drl_env* env, const void* d_keys, void* stream);
 
