@@ -101,12 +101,14 @@ class OnDeviceDQNTrainer:
         self.use_graph = use_graph
         self.step_index = 0
         self.graph = None
+        self._warm = 0
         n, W = env_params.n_drones, env_params.window_size
         self.obs_size = W * W * 6
         dev = self.device
         with torch.cuda.device(dev):
             torch.manual_seed(seed * 1000003 + rank)
             # ---- env (train_jax.py:186-193): rng = PRNGKey(seed); reset with split(rng, N); obs of drone 0 only
+            self._side = torch.cuda.Stream()
             self.env = DeliveryDrones(dev)
             rng = drl_random.PRNGKey(seed)
             self.state = self.env.reset(rng, env_params, num_envs=self.N, env_offset=self.offset, num_envs_global=num_envs_global)
@@ -216,45 +218,37 @@ class OnDeviceDQNTrainer:
             self._call(self.lib.drl_reset(self.h.ptr, _vp(self.keys), s))
             self._call(self.lib.drl_get_obs(self.h.ptr, _vp(self.obs), s))
 
-    def train(self, num_steps: int):
-        """Run ``num_steps`` trainer steps; returns metrics incl. ``obs_per_sec`` (train_jax.py:233-236)."""
-        with torch.cuda.device(self.device):
-            done_steps = 0
-            # eager until the buffer can be sampled (buffer.can_sample, :84-90)
-            while done_steps < num_steps and not self.buffer.can_sample(self.bstate):
-                self._step_body(train=False)
-                self._host_side(self.step_index)
-                self.step_index += 1
-                done_steps += 1
-            if done_steps < num_steps and self.use_graph and self.graph is None:
-                side = torch.cuda.Stream()
-                side.wait_stream(torch.cuda.current_stream())
-                with torch.cuda.stream(side):                     # warm-up outside capture (optimizer state, cuBLAS)
-                    for _ in range(3):
-                        if done_steps >= num_steps:
-                            break
-                        self._step_body(train=True)
-                        self._host_side(self.step_index)
-                        self.step_index += 1
-                        done_steps += 1
-                torch.cuda.current_stream().wait_stream(side)
+    def _can_sample_after_add(self, step):
+        """``buffer.can_sample`` right after this step's ``add_many`` (train_jax.py:84), from host-known counts."""
+        return min((step + 1) * self.N, self.ag.memory_size) >= self.ag.batch_size
+
+    def _one_step(self):
+        train = self._can_sample_after_add(self.step_index)
+        if not (train and self.use_graph):
+            self._step_body(train)
+        elif self._warm < 3:                                      # eager warm-up before capture (optimizer state, cuBLAS)
+            side = self._side
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                self._step_body(True)
+            torch.cuda.current_stream().wait_stream(side)
+            self._warm += 1
+        else:
+            if self.graph is None:
                 torch.cuda.synchronize()
                 self.graph = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(self.graph):
-                    self._step_body(train=True)
-                self.graph.replay()                               # capture enqueued no work: run the step it describes
-                self._host_side(self.step_index)
-                self.step_index += 1
-                done_steps += 1
-            while done_steps < num_steps:
-                if self.graph is not None:
-                    self.graph.replay()
-                else:
-                    self._step_body(train=True)
-                self._host_side(self.step_index)
-                self.step_index += 1
-                done_steps += 1
-        return done_steps
+                with torch.cuda.graph(self.graph):                # capture enqueues no work
+                    self._step_body(True)
+            self.graph.replay()
+        self._host_side(self.step_index)
+        self.step_index += 1
+
+    def train(self, num_steps: int):
+        """Run ``num_steps`` trainer steps (train_jax.py:229 scan); ``timed_train`` adds obs/s (:233-236)."""
+        with torch.cuda.device(self.device):
+            for _ in range(num_steps):
+                self._one_step()
+        return num_steps
 
     def timed_train(self, num_steps: int):
         torch.cuda.synchronize(self.device)
