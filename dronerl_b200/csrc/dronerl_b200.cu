@@ -107,7 +107,7 @@ k_obs_warp(const __grid_constant__ DevCfg c, const uint8_t* __restrict__ ground,
 // ---- CTA-per-env kernels (larger grids) -------------------------------------------------------
 
 template <int NB, class D>
-__global__ void __launch_bounds__(kCtaThreads, 3)
+__global__ void __launch_bounds__(kCtaThreads, DRL_CTA_MIN_BLOCKS)
 k_step_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint32_t* __restrict__ drones,
            const uint32_t* __restrict__ keys, const int8_t* __restrict__ actions, float* __restrict__ rewards,
            uint8_t* __restrict__ dones, float* __restrict__ obs, unsigned long long* __restrict__ stats) {
@@ -120,6 +120,7 @@ k_step_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint3
     Group<T> grp{reinterpret_cast<unsigned long long*>(smem_raw + c.off_red)};
     const Sel sel = carve_sel(smem_raw, c);
     zero_code(c, sm, threadIdx.x, T);
+    if (threadIdx.x == 0) sel.cnt[1] = sel.cnt[2] = 0u;   // rank_positions' pre-filter counters
     const int nvec = c.GS >> 4, n = c.n;
     Stats st;
     unsigned env_steps = 0;
@@ -297,12 +298,14 @@ typedef void (*obs_fn)(DevCfg, const uint8_t*, const uint32_t*, float*);
 
 using D943 = Dims<9, 4, 3>;    // train_jax.py CLI defaults (train_jax.py:338-344)
 using D833 = Dims<8, 3, 3>;    // DroneEnvParams dataclass defaults (jax_impl/env/env.py:13-26)
+using DLW = Dims<64, 32, 5>;   // BASELINE.json large world (config C4)
 
 static int static_shape(const drl_env* e) {
     const DevCfg& c = e->dc;
     if (c.obs_n != c.n) return 0;      // reduced-obs mode runs the dynamic-shape instances
     if (c.G == 9 && c.n == 4 && c.r == 3) return 1;
     if (c.G == 8 && c.n == 3 && c.r == 3) return 2;
+    if (c.G == 64 && c.n == 32 && c.r == 5) return 3;
     return 0;
 }
 template <int NB, class D>
@@ -317,6 +320,7 @@ static step_fn pick_step(const drl_env* e) {
             default: return e->nb == 1 ? step_warp_q<1, DynDims>(e->envs_per_warp) : step_warp_q<2, DynDims>(e->envs_per_warp);
         }
     }
+    if (static_shape(e) == 3) return (step_fn)k_step_cta<(64 * 64 / 2) / kCtaThreads, DLW>;
     return e->nb == 2 ? (step_fn)k_step_cta<2, DynDims> : e->nb == 8 ? (step_fn)k_step_cta<8, DynDims>
                                                                      : (step_fn)k_step_cta<16, DynDims>;
 }
@@ -332,6 +336,7 @@ static obs_fn pick_obs(const drl_env* e) {
             default: return (obs_fn)k_obs_warp<DynDims>;
         }
     }
+    if (static_shape(e) == 3) return (obs_fn)k_obs_cta<DLW>;
     return (obs_fn)k_obs_cta<DynDims>;
 }
 

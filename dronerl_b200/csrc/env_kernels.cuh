@@ -28,7 +28,13 @@ namespace drl {
 constexpr unsigned FULL = 0xFFFFFFFFu;
 enum : int { SKY = 2, STATION = 3, DROPZONE = 4, PACKET = 5 };
 enum : int { A_LEFT = 0, A_DOWN = 1, A_RIGHT = 2, A_UP = 3 };
-constexpr int kCtaThreads = 256;
+#ifndef DRL_CTA_THREADS
+#define DRL_CTA_THREADS 256
+#endif
+#ifndef DRL_CTA_MIN_BLOCKS
+#define DRL_CTA_MIN_BLOCKS 3
+#endif
+constexpr int kCtaThreads = DRL_CTA_THREADS;
 #ifndef DRL_WARPS_PER_BLOCK
 #define DRL_WARPS_PER_BLOCK 8
 #endif
@@ -114,6 +120,7 @@ struct Group {
     static constexpr int kWarps = T / 32;
     unsigned long long* red;   // [2][kWarps] scratch (CTA mode)
     int par = 0;
+    int spar = 0;              // which of the two pre-filter counters the next rank_positions call uses
 
     __device__ __forceinline__ static int tid() { return kWarp ? (int)(threadIdx.x & 31) : (int)threadIdx.x; }
     __device__ __forceinline__ static void sync() {
@@ -320,9 +327,9 @@ __device__ __forceinline__ Sel carve_sel(unsigned char* base, const DevCfg& c) {
 
 // sel.pos[0 .. J) = positions of jax.lax.top_k(log(cand) + noise, J) in rank order; ends with a barrier.
 template <int T, int NB, class D>
-__device__ __forceinline__ void rank_positions(Group<T>& grp, const D& d, const Sel& sel, int tid,
-                                               const uint32_t (&mant)[2 * NB], uint32_t candm, uint32_t validm, int J) {
-    static_assert(T >= 256 && T % 32 == 0, "CTA mode");
+__device__ __forceinline__ void rank_positions_hist(Group<T>& grp, const D& d, const Sel& sel, int tid,
+                                                    const uint32_t (&mant)[2 * NB], uint32_t candm, uint32_t validm, int J) {
+    static_assert(T >= 128 && T % 32 == 0, "CTA mode");
     const int lane = tid & 31;
     // Only the top of the mantissa range can hold the J winners: histogram bins >= B0 first (about 8 J keys
     // expected there when half the grid is a candidate), everything only if that was too few.
@@ -396,6 +403,64 @@ __device__ __forceinline__ void rank_positions(Group<T>& grp, const D& d, const 
     __syncthreads();
 }
 
+// Fast path for the few ranks a step needs (J <= 64): the J winners of ``ncand`` uniform mantissas all lie in the
+// top ~ (J + 4 sqrt(J) + 8) / ncand of the range with overwhelming probability, so one compare per slot
+// gathers that sliver straight into the list and the survivors are ranked by counting, four threads per key.
+// Too few survivors (the estimate was off, or the -inf tail is needed) or too many: the histogram path above
+// redoes the selection -- the result is exact either way because ranking compares full keys.
+template <int T, int NB, class D>
+__device__ __forceinline__ void rank_positions(Group<T>& grp, const D& d, const Sel& sel, int tid,
+                                               const uint32_t (&mant)[2 * NB], uint32_t candm, uint32_t validm, int J,
+                                               int ncand) {
+    if (J > 64 || sel.cap < 128) {
+        rank_positions_hist<T, NB>(grp, d, sel, tid, mant, candm, validm, J);
+        return;
+    }
+    int sq = 1;
+    while (sq * sq < J) ++sq;
+    const int target = J + 4 * sq + 8;                      // <= 104
+    uint32_t T0 = 0;
+    if (ncand > target) T0 = (uint32_t)(8388608.0f * (1.0f - __fdividef((float)target, (float)ncand)));
+    // cnt[1], cnt[2] alternate as this path's counter: the one in use is zero on entry (both are zeroed at kernel
+    // start); thread 0 re-zeroes the OTHER one, which nobody touches during this call
+    uint32_t* const counter = sel.cnt + 1 + grp.spar;
+    if (tid == 0) sel.cnt[1 + (grp.spar ^ 1)] = 0u;
+    grp.spar ^= 1;
+    uint32_t hits = 0;
+#pragma unroll
+    for (int s = 0; s < 2 * NB; ++s) hits |= (mant[s] >= T0 ? 1u : 0u) << s;
+    hits &= candm;
+    if (hits) {                                             // rare: ~target / T threads get here
+#pragma unroll
+        for (int s = 0; s < 2 * NB; ++s)
+            if ((hits >> s) & 1u) {
+                const uint32_t i = atomicAdd(counter, 1u);
+                if (i < 128u)
+                    sel.list[i] = ((unsigned long long)(mant[s] + 1u) << 16) | (unsigned)(d.G2() - slot_cell<T, NB>(tid, s, d.H()));
+            }
+    }
+    __syncthreads();
+    const int m = (int)*counter;
+    if (m >= J && m <= 128) {
+        // key kq of thread quad (tid >> 2); the four threads of a quad split the list.  The loop bound is
+        // uniform over the CTA so that every lane reaches the shuffles.
+        for (int base = 0; base < m; base += T / 4) {
+            const int kq = base + (tid >> 2);
+            const bool live = kq < m;
+            const unsigned long long key = live ? sel.list[kq] : 0ull;
+            int r = 0;
+            if (live)
+                for (int u = tid & 3; u < m; u += 4) r += sel.list[u] > key;
+            r += __shfl_xor_sync(FULL, r, 1);
+            r += __shfl_xor_sync(FULL, r, 2);
+            if (live && (tid & 3) == 0 && r < J) sel.pos[r] = (uint16_t)(d.G2() - (int)(key & 0xFFFFull));
+        }
+        __syncthreads();
+    } else {
+        rank_positions_hist<T, NB>(grp, d, sel, tid, mant, candm, validm, J);
+    }
+}
+
 // ---- TMA bulk store of an obs tile ------------------------------------------------------------
 
 // Two tile buffers alternate per warp; bulk groups complete in order, so "at most one group still
@@ -450,51 +515,60 @@ __device__ __forceinline__ void compose_tile(const D& d, const Smem& sm, int d0,
     const int max_rows = d.tile_drones() * W;
     const int lpr = max_rows <= 8 ? 4 : max_rows <= 16 ? 2 : 1;
     const int items = rows * lpr;
-    // channel of cell wx of window row ``row`` (0 = nothing to store)
-    auto row_codes = [&](int item) -> uint32_t {
+    // channel of cell wx of window row ``row`` (0 = nothing to store), 3 bits per cell packed into a P
+    auto row_codes = [&](int item, auto zero) {
+        using P = decltype(zero);
         const int row = item / lpr, sl = item - row * lpr;
         const int dd = (int)d.divW((uint32_t)row);
         const int wy = row - dd * W;
         const uint32_t rec = sm.sdr[d0 + dd];
         const int gy = (int)((rec >> 8) & 0xFFu) + wy - d.r();
         const int gx0 = (int)(rec & 0xFFu) - d.r();
-        uint32_t packed = 0;
+        P packed = 0;
         if ((unsigned)gy >= (unsigned)G) {
-            for (int wx = sl, j = 0; wx < W; wx += lpr, ++j) packed |= 5u << (3 * j);     // the whole row is wall
+            for (int wx = sl, j = 0; wx < W; wx += lpr, ++j) packed |= (P)5u << (3 * j);     // the whole row is wall
         } else {
             const uint8_t* grow = sm.sg + gy * G;
             for (int wx = sl, j = 0; wx < W; wx += lpr, ++j) {
                 const int gx = gx0 + wx;
                 const uint32_t g = (unsigned)gx < (unsigned)G ? grow[gx] : (uint32_t)SKY;
-                packed |= ((kChan >> (4u * g)) & 7u) << (3 * j);
+                packed |= (P)((kChan >> (4u * g)) & 7u) << (3 * j);
             }
         }
         return packed;
     };
-    auto row_emit = [&](int item, uint32_t packed) {
+    auto row_emit = [&](int item, auto packed) {
         const int row = item / lpr, sl = item - row * lpr;
         float* o = tile + row * W * 6;
         for (int wx = sl; wx < W; wx += lpr, packed >>= 3) {
-            const uint32_t ch = packed & 7u;
+            const uint32_t ch = (uint32_t)packed & 7u;
             if (ch) o[wx * 6 + ch] = 1.0f;
         }
     };
     // Window analysis does not touch the tile, so it runs BEFORE waiting for the previous bulk store to
-    // release the buffer (up to two rows per lane, ten 3-bit codes per row, kept in registers).
-    const bool packed_path = items <= 64 && (W + lpr - 1) / lpr <= 10;
+    // release the buffer: up to two rows per lane with ten 3-bit codes each in 32-bit registers, or one row
+    // per lane with up to 21 codes in a 64-bit pair (radius-5 windows of the large world).
+    const int cpi = (W + lpr - 1) / lpr;                    // cells per item
+    const bool packed32 = items <= 64 && cpi <= 10;
+    const bool packed64 = !packed32 && items <= 32 && cpi <= 21;
     uint32_t p0 = 0, p1 = 0;
-    if (packed_path) {
-        if (lane < items) p0 = row_codes(lane);
-        if (lane + 32 < items) p1 = row_codes(lane + 32);
+    unsigned long long pw = 0;
+    if (packed32) {
+        if (lane < items) p0 = row_codes(lane, 0u);
+        if (lane + 32 < items) p1 = row_codes(lane + 32, 0u);
+    } else if (packed64) {
+        if (lane < items) pw = row_codes(lane, 0ull);
     }
     tile_wait_reusable(lane, bufs);
     const int vecs = (nd * d.W2() * 24 + 15) >> 4;          // tile buffers are padded to 128 B
     float4* t4 = reinterpret_cast<float4*>(tile);
     for (int i = lane; i < vecs; i += 32) t4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     __syncwarp();
-    if (packed_path) {
+    if (packed32) {
         if (lane < items) row_emit(lane, p0);
         if (lane + 32 < items) row_emit(lane + 32, p1);
+    } else if (packed64) {
+        if (lane < items) row_emit(lane, pw);
     } else {
         for (int item = lane; item < items; item += 32) {      // big windows / many rows: cell by cell
             const int row = item / lpr, sl = item - row * lpr;
@@ -680,7 +754,7 @@ __device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const D
         scan_free();
         ensure_noise();
         const int J = F1 < k ? k : 32 - __clz(mP);
-        rank_positions<T, NB>(grp, d, sel, tid, mant, freem, validm, J);
+        rank_positions<T, NB>(grp, d, sel, tid, mant, freem, validm, J, F1);
         // grid.at[pos].set(fill): rank j takes fill[j]; the cells are distinct, so all ranks write at once
         for (int j = tid; j < J; j += T) sm.sg[sel.pos[j]] = (j < n && ((mP >> j) & 1u)) ? PACKET : 0;
     }
@@ -694,7 +768,7 @@ __device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const D
             if (F2 < k) capture_oldsky();
             ensure_noise();
             const int J = F2 < k ? k : 32 - __clz(mD);
-            rank_positions<T, NB>(grp, d, sel, tid, mant, freem, validm, J);
+            rank_positions<T, NB>(grp, d, sel, tid, mant, freem, validm, J, F2);
             for (int j = tid; j < J; j += T) sm.sg[sel.pos[j]] = (j < n && ((mD >> j) & 1u)) ? DROPZONE : 0;
         }
     }
@@ -712,7 +786,7 @@ __device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const D
         for (int s = 0; s < 2 * NB; ++s)
             if (slot_cell<T, NB>(tid, s, d.H()) == G2 - 1) candm &= ~(1u << s);
         noise_mantissas<T, NB>(tid, d, sk0, sk1, mant);
-        rank_positions<T, NB>(grp, d, sel, tid, mant, candm, validm, 32 - __clz(mDone));
+        rank_positions<T, NB>(grp, d, sel, tid, mant, candm, validm, 32 - __clz(mDone), G2 - 1 - c.k_reset[3] - n);
         if (drone_warp && surv) sm.code[x * G + y] = 0;     // restore the all-zero invariant
         if (drone_warp && done) {
             const int pos = sel.pos[lane];
@@ -755,7 +829,7 @@ __device__ __forceinline__ void env_reset(Group<T>& grp, const DevCfg& c, const 
                 if (tid == 0) sm.sg[pos] = (uint8_t)obj;
             });
         } else {
-            rank_positions<T, NB>(grp, d, sel, tid, mant, freem, validm, c.k_reset[t]);
+            rank_positions_hist<T, NB>(grp, d, sel, tid, mant, freem, validm, c.k_reset[t]);
             for (int j = tid; j < c.k_reset[t]; j += T) sm.sg[sel.pos[j]] = (uint8_t)obj;
         }
         Group<T>::sync();
@@ -776,7 +850,7 @@ __device__ __forceinline__ void env_reset(Group<T>& grp, const DevCfg& c, const 
             }
         });
     } else {
-        rank_positions<T, NB>(grp, d, sel, tid, mant, candm, validm, n);
+        rank_positions_hist<T, NB>(grp, d, sel, tid, mant, candm, validm, n);
         if (drone_warp && lane < n) {
             const int pos = sel.pos[lane];
             x = (int)d.divG((uint32_t)pos);

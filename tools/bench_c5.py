@@ -64,8 +64,12 @@ def main():
                        'num_envs_global': N},
             'loss': float(tr.loss.item()), 'epsilon': float(tr.epsilon.item()),
             'published_reference': 'README.md:73-88 (JAX --use_sharding, other hardware); see BASELINE.md'}), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    # a captured graph holding NCCL work must die before the communicator; skip the collective teardown
+    # altogether (it hung a whole 8-GPU box once): results are printed, leave hard
+    tr.graph = None
+    torch.cuda.synchronize()
+    sys.stdout.flush()
+    os._exit(0)
 
 
 if __name__ == '__main__':
