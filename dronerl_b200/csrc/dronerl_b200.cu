@@ -114,37 +114,38 @@ k_step_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint3
     extern __shared__ __align__(128) unsigned char smem_raw[];
     constexpr int T = kCtaThreads;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const Smem sm = carve(smem_raw, c);
+    const Smem sm0 = carve(smem_raw, c);
     float* tile = reinterpret_cast<float*>(smem_raw + c.off_tile + (size_t)warp * c.tile_bufs * c.tile_stride);
     int tsel = 0;
     Group<T> grp{reinterpret_cast<unsigned long long*>(smem_raw + c.off_red)};
     const Sel sel = carve_sel(smem_raw, c);
-    zero_code(c, sm, threadIdx.x, T);
+    zero_code(c, sm0, threadIdx.x, T);
     if (threadIdx.x == 0) sel.cnt[1] = sel.cnt[2] = 0u;   // rank_positions' pre-filter counters
-    const int nvec = c.GS >> 4, n = c.n;
     Stats st;
     unsigned env_steps = 0;
     const D d{c};
+    const int GS = d.GS(), nvec = GS >> 4, n = d.n();
     const uint32_t validm = valid_slots<T, NB>(threadIdx.x, d);
     __syncthreads();
     for (long long e = blockIdx.x; e < c.N; e += gridDim.x) {
+        const Smem sm = sm0;
         int zc = 0;
         for (int i = threadIdx.x; i < nvec; i += T) {
-            const uint4 v = reinterpret_cast<const uint4*>(ground + e * c.GS)[i];
+            const uint4 v = reinterpret_cast<const uint4*>(ground + e * GS)[i];
             reinterpret_cast<uint4*>(sm.sg)[i] = v;
             zc += zero_bytes16(v);
         }
         uint32_t rec = 0;
         int act = 4;
-        if (threadIdx.x < n) {
+        if ((int)threadIdx.x < n) {
             rec = drones[e * n + threadIdx.x];
             act = actions[e * n + threadIdx.x];
         }
         const uint2 kk = *reinterpret_cast<const uint2*>(keys + 2 * e);
-        const int F0 = grp.sum(zc) - (c.GS - c.G2);     // block-wide: also publishes the ground stores
+        const int F0 = grp.sum(zc) - (GS - d.G2());
         env_step<T, NB>(grp, c, d, sm, sel, validm, F0, rec, act, kk.x, kk.y, rewards + e * n, dones + e * n, st);
         for (int i = threadIdx.x; i < nvec; i += T)
-            reinterpret_cast<uint4*>(ground + e * c.GS)[i] = reinterpret_cast<const uint4*>(sm.sg)[i];
+            reinterpret_cast<uint4*>(ground + e * GS)[i] = reinterpret_cast<const uint4*>(sm.sg)[i];
         if (threadIdx.x < n) drones[e * n + threadIdx.x] = rec;
         if (obs != nullptr) {
             if (warp == 0) obs_publish(d, sm, lane, rec);

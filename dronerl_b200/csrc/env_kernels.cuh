@@ -426,18 +426,22 @@ __device__ __forceinline__ void rank_positions(Group<T>& grp, const D& d, const 
     uint32_t* const counter = sel.cnt + 1 + grp.spar;
     if (tid == 0) sel.cnt[1 + (grp.spar ^ 1)] = 0u;
     grp.spar ^= 1;
+    // Hits are rare (~target / T per thread), so instead of a branch per slot every thread extracts its first
+    // hit with selects, and only warps where some lane has a second one go round again.
     uint32_t hits = 0;
 #pragma unroll
     for (int s = 0; s < 2 * NB; ++s) hits |= (mant[s] >= T0 ? 1u : 0u) << s;
     hits &= candm;
-    if (hits) {                                             // rare: ~target / T threads get here
+    while (__any_sync(FULL, hits != 0u)) {
+        const int hs = __ffs(hits) - 1;                     // -1: nothing (left) in this thread
+        uint32_t hm = 0;
 #pragma unroll
-        for (int s = 0; s < 2 * NB; ++s)
-            if ((hits >> s) & 1u) {
-                const uint32_t i = atomicAdd(counter, 1u);
-                if (i < 128u)
-                    sel.list[i] = ((unsigned long long)(mant[s] + 1u) << 16) | (unsigned)(d.G2() - slot_cell<T, NB>(tid, s, d.H()));
-            }
+        for (int s = 0; s < 2 * NB; ++s) hm = hs == s ? mant[s] : hm;
+        if (hs >= 0) {
+            const uint32_t i = atomicAdd(counter, 1u);
+            if (i < 128u) sel.list[i] = ((unsigned long long)(hm + 1u) << 16) | (unsigned)(d.G2() - slot_cell<T, NB>(tid, hs, d.H()));
+            hits &= hits - 1;
+        }
     }
     __syncthreads();
     const int m = (int)*counter;
@@ -509,6 +513,7 @@ __device__ __forceinline__ void compose_tile(const D& d, const Smem& sm, int d0,
     const int nd = d1 - d0;
     // ground value -> channel: 0 -> none, SKY 2 -> 5, STATION 3 -> 3, DROPZONE 4 -> 2, PACKET 5 -> 1
     constexpr uint32_t kChan = (5u << 8) | (3u << 12) | (2u << 16) | (1u << 20);
+    constexpr uint32_t kLutLo = (5u << 16) | (3u << 24), kLutHi = 2u | (1u << 8);   // the same table, one byte per value (PRMT)
     const int W = d.W(), G = d.G();
     const int rows = nd * W;
     // lanes per window row: keep the warp busy when a tile has few rows
@@ -532,7 +537,7 @@ __device__ __forceinline__ void compose_tile(const D& d, const Smem& sm, int d0,
             for (int wx = sl, j = 0; wx < W; wx += lpr, ++j) {
                 const int gx = gx0 + wx;
                 const uint32_t g = (unsigned)gx < (unsigned)G ? grow[gx] : (uint32_t)SKY;
-                packed |= (P)((kChan >> (4u * g)) & 7u) << (3 * j);
+                packed |= (P)__byte_perm(kLutLo, kLutHi, g) << (3 * j);
             }
         }
         return packed;
