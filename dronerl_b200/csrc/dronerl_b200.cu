@@ -14,6 +14,10 @@
 
 using namespace drl;
 
+#ifndef DRL_QMAX
+#define DRL_QMAX 8       // envs per warp for n_drones <= 4 (4 or 8)
+#endif
+
 // =================================================================================================
 // kernels
 // =================================================================================================
@@ -311,13 +315,14 @@ static int static_shape(const drl_env* e) {
 }
 template <int NB, class D>
 static step_fn step_warp_q(int q) {
-    return q == 4 ? (step_fn)k_step_warp<NB, 4, D> : q == 2 ? (step_fn)k_step_warp<NB, 2, D> : (step_fn)k_step_warp<NB, 1, D>;
+    return q == DRL_QMAX && q == 8 ? (step_fn)k_step_warp<NB, DRL_QMAX, D> : q == 4 ? (step_fn)k_step_warp<NB, 4, D>
+         : q == 2 ? (step_fn)k_step_warp<NB, 2, D> : (step_fn)k_step_warp<NB, 1, D>;
 }
 static step_fn pick_step(const drl_env* e) {
     if (e->warp_mode) {
         switch (static_shape(e)) {
-            case 1: return (step_fn)k_step_warp<2, 4, D943>;
-            case 2: return (step_fn)k_step_warp<1, 4, D833>;
+            case 1: return (step_fn)k_step_warp<2, DRL_QMAX, D943>;
+            case 2: return (step_fn)k_step_warp<1, DRL_QMAX, D833>;
             default: return e->nb == 1 ? step_warp_q<1, DynDims>(e->envs_per_warp) : step_warp_q<2, DynDims>(e->envs_per_warp);
         }
     }
@@ -462,13 +467,13 @@ int drl_create(const drl_config* cfg, drl_env** out) {
     c.ntiles = (n + c.tile_drones - 1) / c.tile_drones;
     c.tile_stride = round_up(c.tile_drones * cell_bytes, 128);
     c.tile_bufs = 1;
-    e->envs_per_warp = !e->warp_mode ? 1 : n <= 8 ? 4 : n <= 16 ? 2 : 1;
+    e->envs_per_warp = !e->warp_mode ? 1 : n <= 4 ? DRL_QMAX : n <= 8 ? 4 : n <= 16 ? 2 : 1;
     const int Q = e->envs_per_warp;
     c.off_code = (e->warp_mode ? 2 : 1) * Q * c.GS;  // warp step kernel: two staging buffers of Q ground rows
     c.off_sdr = c.off_code + Q * round_up((int)G2, 16);
     c.off_sdf = c.off_sdr + 128;
     c.off_misc = c.off_sdf + 128;
-    c.off_rec = c.off_misc + 16;                    // [2][32] staged drone records
+    c.off_rec = c.off_misc + 32;                    // [2][32] staged drone records
     c.off_key = c.off_rec + 256;                    // [2][Q][2] staged keys
     c.off_red = c.off_key + 64;
     c.off_sel = round_up(c.off_red + 2 * (kCtaThreads / 32) * 8, 16);

@@ -2,7 +2,7 @@
 //
 // The per-drone part of a step (move, collisions, charge, pickup/delivery, rewards) needs only
 // n lanes, and the two key splits only 2, so a warp runs them for Q = 4 (n <= 8), 2 (n <= 16) or 1
-// envs at once: env q of the group owns lanes [q*S, (q+1)*S), S = 32/Q; match_any keys and ballots
+// envs at once (8 for n <= 4): env q of the group owns lanes [q*S, (q+1)*S), S = 32/Q; match_any keys and ballots
 // are segmented by q.  What needs the whole warp -- threefry noise over the grid, rank extraction,
 // observation tiles -- then runs env by env, and only for the envs that need it.
 // Semantics: /root/reference/jax_impl/env/env.py:137-250 (step) and :274-309 (get_obs).
@@ -11,8 +11,9 @@
 
 namespace drl {
 
+template <int NV>
 struct GroupInputs {   // inputs of one group of Q envs, prefetched one group ahead
-    uint4 gv;
+    uint4 gv[NV];      // ground vectors lane, lane + 32, ... of the group's Q consecutive rows
     uint32_t rec, k0, k1;
     int act;
 };
@@ -49,19 +50,23 @@ __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsi
         uint32_t* w = reinterpret_cast<uint32_t*>(code_all);
         for (int i = lane; i < (Q * CP) >> 2; i += 32) w[i] = 0u;
     }
-    const int nvec = GS >> 4;                     // 16-byte vectors per ground row; Q * nvec <= 32
+    const int nvec = GS >> 4;                     // 16-byte vectors per ground row; Q * nvec <= 32 * NV
+    constexpr int NV = Q > 4 ? 2 : 1;
+    const uint32_t inv_nvec = 65536u / (uint32_t)nvec + 1u;   // v / nvec == (v * inv_nvec) >> 16 for v < 64
     const uint32_t validm = valid_slots<32, NB>(lane, d);
     const int k = c.k_spawn;
     Stats st;
     unsigned env_steps = 0;
     int tsel = 0;
 
-    GroupInputs nxt = {};
+    GroupInputs<NV> nxt = {};
     auto prefetch = [&](long long g) {
         const long long e0 = g * Q;
         if (e0 < c.N) {
             const int nq = (int)min((long long)Q, c.N - e0);
-            if (lane < nvec * nq) nxt.gv = reinterpret_cast<const uint4*>(ground + e0 * GS)[lane];
+#pragma unroll
+            for (int v = 0; v < NV; ++v)
+                if (lane + 32 * v < nvec * nq) nxt.gv[v] = reinterpret_cast<const uint4*>(ground + e0 * GS)[lane + 32 * v];
             if (sub < nq) {
                 if (li < n) {
                     nxt.rec = drones[(e0 + sub) * n + li];
@@ -78,7 +83,7 @@ __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsi
     for (; g * Q < c.N; g += group_stride) {
         const long long e0 = g * Q;
         const int nq = (int)min((long long)Q, c.N - e0);
-        const GroupInputs cur = nxt;
+        const GroupInputs<NV> cur = nxt;
         prefetch(g + group_stride);
         const bool act_env = sub < nq;
         const bool isd = act_env && li < n;
@@ -86,11 +91,11 @@ __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsi
 
         // ---- stage the ground rows of the group, count free cells per env ---------------------------
         __syncwarp();
-        {
+        if constexpr (NV == 1) {
             int zc = 0;
             if (lane < nvec * nq) {
-                reinterpret_cast<uint4*>(sg_all)[lane] = cur.gv;
-                zc = zero_bytes16(cur.gv);
+                reinterpret_cast<uint4*>(sg_all)[lane] = cur.gv[0];
+                zc = zero_bytes16(cur.gv[0]);
             }
             if constexpr (Q == 1) {
                 zc = (int)__reduce_add_sync(FULL, (unsigned)zc);
@@ -104,6 +109,18 @@ __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsi
                         const int r = (int)__reduce_add_sync(m, (unsigned)zc);
                         if (lane == q * nvec) zcs[q] = r;
                     }
+                }
+            }
+        } else {
+            // rows straddle the two passes: per-env counts by shared-memory atomics
+            if (lane < Q) zcs[lane] = 0;
+            __syncwarp();
+#pragma unroll
+            for (int v = 0; v < NV; ++v) {
+                const int vi = lane + 32 * v;
+                if (vi < nvec * nq) {
+                    reinterpret_cast<uint4*>(sg_all)[vi] = cur.gv[v];
+                    atomicAdd(&zcs[((uint32_t)vi * inv_nvec) >> 16], zero_bytes16(cur.gv[v]));
                 }
             }
         }
@@ -281,7 +298,10 @@ __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsi
 
         // ---- write back, observations -----------------------------------------------------------------
         const uint32_t rec = (uint32_t)rx | ((uint32_t)ry << 8) | ((uint32_t)carry << 16) | ((uint32_t)ch << 24);
-        if (lane < nvec * nq) reinterpret_cast<uint4*>(ground + e0 * GS)[lane] = reinterpret_cast<const uint4*>(sg_all)[lane];
+#pragma unroll
+        for (int v = 0; v < NV; ++v)
+            if (lane + 32 * v < nvec * nq)
+                reinterpret_cast<uint4*>(ground + e0 * GS)[lane + 32 * v] = reinterpret_cast<const uint4*>(sg_all)[lane + 32 * v];
         if (isd) drones[e * n + li] = rec;
         if (obs != nullptr) {
             // sdr[lane] = record | owns-its-cell << 17 (highest drone index per cell shows its charge)
