@@ -327,12 +327,13 @@ static step_fn pick_step(const drl_env* e) {
         }
     }
     if (static_shape(e) == 3) return (step_fn)k_step_cta<(64 * 64 / 2) / kCtaThreads, DLW>;
-    return e->nb == 2 ? (step_fn)k_step_cta<2, DynDims> : e->nb == 8 ? (step_fn)k_step_cta<8, DynDims>
-                                                                     : (step_fn)k_step_cta<16, DynDims>;
+    return e->nb == 2 ? (step_fn)k_step_cta<2, DynDims> : e->nb == 4 ? (step_fn)k_step_cta<4, DynDims>
+         : e->nb == 8 ? (step_fn)k_step_cta<8, DynDims> : (step_fn)k_step_cta<16, DynDims>;
 }
 static reset_fn pick_reset(const drl_env* e) {
     if (e->warp_mode) return e->nb == 1 ? (reset_fn)k_reset_warp<1> : (reset_fn)k_reset_warp<2>;
-    return e->nb == 2 ? (reset_fn)k_reset_cta<2> : e->nb == 8 ? (reset_fn)k_reset_cta<8> : (reset_fn)k_reset_cta<16>;
+    return e->nb == 2 ? (reset_fn)k_reset_cta<2> : e->nb == 4 ? (reset_fn)k_reset_cta<4> : e->nb == 8 ? (reset_fn)k_reset_cta<8>
+                                                                                            : (reset_fn)k_reset_cta<16>;
 }
 static obs_fn pick_obs(const drl_env* e) {
     if (e->warp_mode) {
@@ -461,7 +462,7 @@ int drl_create(const drl_config* cfg, drl_env** out) {
 
     e->warp_mode = G2 <= 128;
     const int cell_bytes = c.W2 * 24;
-    e->nb = e->warp_mode ? (c.H <= 32 ? 1 : 2) : (c.H <= 2 * kCtaThreads ? 2 : c.H <= 8 * kCtaThreads ? 8 : 16);
+    e->nb = e->warp_mode ? (c.H <= 32 ? 1 : 2) : (c.H <= 2 * kCtaThreads ? 2 : c.H <= 4 * kCtaThreads ? 4 : c.H <= 8 * kCtaThreads ? 8 : 16);
     c.tile_drones = tile_drones_for(n, c.W2, e->warp_mode);
     c.obs_n = n;
     c.ntiles = (n + c.tile_drones - 1) / c.tile_drones;
