@@ -114,7 +114,9 @@ template <int NB, class D>
 __global__ void __launch_bounds__(kCtaThreads, DRL_CTA_MIN_BLOCKS)
 k_step_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint32_t* __restrict__ drones,
            const uint32_t* __restrict__ keys, const int8_t* __restrict__ actions, float* __restrict__ rewards,
-           uint8_t* __restrict__ dones, float* __restrict__ obs, unsigned long long* __restrict__ stats) {
+           uint8_t* __restrict__ dones, float* __restrict__ obs, unsigned long long* __restrict__ stats, int* redo, const int* redo_list) {
+    // ``redo`` == nullptr: step every env of the slice.  Otherwise step only the envs the fast kernel gave up on:
+    // redo[0] = how many, redo[1] = exit ticket, redo_list = their local indices.
     extern __shared__ __align__(128) unsigned char smem_raw[];
     constexpr int T = kCtaThreads;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -131,7 +133,9 @@ k_step_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint3
     const int GS = d.GS(), nvec = GS >> 4, n = d.n();
     const uint32_t validm = valid_slots<T, NB>(threadIdx.x, d);
     __syncthreads();
-    for (long long e = blockIdx.x; e < c.N; e += gridDim.x) {
+    const long long work = redo ? (long long)redo[0] : c.N;
+    for (long long w = blockIdx.x; w < work; w += gridDim.x) {
+        const long long e = redo ? (long long)redo_list[w] : w;
         const Smem sm = sm0;
         int zc = 0;
         for (int i = threadIdx.x; i < nvec; i += T) {
@@ -158,6 +162,81 @@ k_step_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint3
             __syncthreads();
         }
         if (threadIdx.x == 0) ++env_steps;
+    }
+    tile_drain(lane);
+    if (warp == 0) flush_stats(st, env_steps, stats, lane);
+    if (redo != nullptr) {          // the last CTA out re-arms the list for the next step
+        __syncthreads();
+        if (threadIdx.x == 0 && atomicAdd(redo + 1, 1) == (int)gridDim.x - 1) {
+            redo[0] = 0;
+            redo[1] = 0;
+            __threadfence();
+        }
+    }
+}
+
+// Fast path of the CTA-mode step (see env_step_fast): TF threads per env, nothing of a noise vector kept in
+// registers.  Envs it cannot finish are appended to ``redo`` untouched and stepped by k_step_cta right after.
+#ifndef DRL_FAST_THREADS
+#define DRL_FAST_THREADS 256
+#endif
+#ifndef DRL_FAST_MIN_BLOCKS
+#define DRL_FAST_MIN_BLOCKS 4
+#endif
+constexpr int kFastThreads = DRL_FAST_THREADS;
+
+template <int NB, class D>
+__global__ void __launch_bounds__(kFastThreads, DRL_FAST_MIN_BLOCKS)
+k_step_fast(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint32_t* __restrict__ drones,
+            const uint32_t* __restrict__ keys, const int8_t* __restrict__ actions, float* __restrict__ rewards,
+            uint8_t* __restrict__ dones, float* __restrict__ obs, unsigned long long* __restrict__ stats, int* redo, int* redo_list) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr int T = kFastThreads;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const Smem sm = carve(smem_raw, c);
+    float* tile = reinterpret_cast<float*>(smem_raw + c.off_tile + (size_t)warp * c.tile_bufs * c.tile_stride);
+    int tsel = 0;
+    Group<T> grp{reinterpret_cast<unsigned long long*>(smem_raw + c.off_red)};
+    const Sel sel = carve_sel(smem_raw, c);
+    zero_code(c, sm, threadIdx.x, T);
+    if (threadIdx.x == 0) sel.cnt[1] = sel.cnt[2] = 0u;
+    Stats st;
+    unsigned env_steps = 0;
+    const D d{c};
+    const int GS = d.GS(), nvec = GS >> 4, n = d.n();
+    __syncthreads();
+    for (long long e = blockIdx.x; e < c.N; e += gridDim.x) {
+        int zc = 0;
+        for (int i = threadIdx.x; i < nvec; i += T) {
+            const uint4 v = reinterpret_cast<const uint4*>(ground + e * GS)[i];
+            reinterpret_cast<uint4*>(sm.sg)[i] = v;
+            zc += zero_bytes16(v);
+        }
+        uint32_t rec = 0;
+        int act = 4;
+        if ((int)threadIdx.x < n) {
+            rec = drones[e * n + threadIdx.x];
+            act = actions[e * n + threadIdx.x];
+        }
+        const uint2 kk = *reinterpret_cast<const uint2*>(keys + 2 * e);
+        const int F0 = grp.sum(zc) - (GS - d.G2());
+        const Stats before = st;
+        const bool ok = env_step_fast<T, NB>(grp, c, d, sm, sel, F0, rec, act, kk.x, kk.y, rewards + e * n, dones + e * n, st);
+        if (ok) {
+            for (int i = threadIdx.x; i < nvec; i += T)
+                reinterpret_cast<uint4*>(ground + e * GS)[i] = reinterpret_cast<const uint4*>(sm.sg)[i];
+            if ((int)threadIdx.x < n) drones[e * n + threadIdx.x] = rec;
+            if (obs != nullptr) {
+                if (warp == 0) obs_publish(d, sm, lane, rec);
+                __syncthreads();
+                obs_tiles(d, c, sm, obs, e, tile, tsel, warp, T / 32, lane);
+            }
+            if (threadIdx.x == 0) ++env_steps;
+        } else {
+            st = before;
+            if (threadIdx.x == 0) redo_list[atomicAdd(redo, 1)] = (int)e;
+        }
+        __syncthreads();
     }
     tile_drain(lane);
     if (warp == 0) flush_stats(st, env_steps, stats, lane);
@@ -275,6 +354,10 @@ struct drl_env {
     cudaStream_t pipe_stream[2];
     cudaEvent_t pipe_begin, pipe_end[2];
     int per_sm_step;      // resident step CTAs per SM (grid sizing of chunk launches)
+    int use_fast;         // CTA mode: run the streamed-selection kernel first, the general one on its redo list
+    int per_sm_fast;
+    DevCfg fast_dc;       // the fast kernel's shared-memory layout (otherwise equal to dc)
+    int* d_redo;          // [64] headers (4 ints per concurrent launch slot) + [N] redo list
     int smem_optin;       // device limit of opt-in dynamic shared memory per CTA
     char err[512];
 };
@@ -296,8 +379,26 @@ static int fail(drl_env* env, int code, const char* fmt, const char* a = "", lon
 static uint32_t magic(int d) { return d <= 1 ? 0u : (uint32_t)((1ull << 32) / (unsigned)d + 1ull); }
 static int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
+// Shared-memory carve-up of one group (a warp in warp mode, the CTA in CTA mode).  ``fast``: the streamed-selection
+// kernel's leaner layout -- survivor marks as a bitmap instead of a byte grid, no histogram, a 128-entry key list.
+static void carve_layout(DevCfg& c, bool warp_mode, int Q, bool fast, int cta_threads) {
+    c.off_code = Q * c.GS;
+    c.off_sdr = c.off_code + (fast ? round_up((c.G2 + 31) / 32 * 4, 16) : Q * round_up(c.G2, 16));
+    c.off_sdf = c.off_sdr + 128;
+    c.off_misc = c.off_sdf + 128;
+    c.off_red = c.off_misc + 32;
+    c.off_sel = round_up(c.off_red + (warp_mode ? 0 : 2 * (cta_threads / 32) * 8), 16);
+    c.sel_hist = fast ? 0 : 1024;
+    c.sel_cap = fast ? 128 : c.sel_maxj + 256;      // J keys plus a generous few histogram bins' worth
+    // CTA mode only: histogram [256] | counters [4] | key list [cap] | rank -> position table [maxj]
+    const int sel_bytes = warp_mode ? 0 : c.sel_hist + 16 + c.sel_cap * 8 + round_up(c.sel_maxj * 2, 16);
+    c.off_tile = round_up(c.off_sel + sel_bytes, 128);
+    c.group_bytes = c.off_tile + c.tile_bufs * c.tile_stride * (warp_mode ? 1 : cta_threads / 32);
+}
+
 typedef void (*step_fn)(DevCfg, uint8_t*, uint32_t*, const uint32_t*, const int8_t*, float*, uint8_t*, float*,
                         unsigned long long*);
+
 typedef void (*reset_fn)(DevCfg, uint8_t*, uint32_t*, const uint32_t*, unsigned long long*);
 typedef void (*obs_fn)(DevCfg, const uint8_t*, const uint32_t*, float*);
 
@@ -318,17 +419,33 @@ static step_fn step_warp_q(int q) {
     return q == DRL_QMAX && q == 8 ? (step_fn)k_step_warp<NB, DRL_QMAX, D> : q == 4 ? (step_fn)k_step_warp<NB, 4, D>
          : q == 2 ? (step_fn)k_step_warp<NB, 2, D> : (step_fn)k_step_warp<NB, 1, D>;
 }
-static step_fn pick_step(const drl_env* e) {
+static const void* pick_step(const drl_env* e) {
     if (e->warp_mode) {
         switch (static_shape(e)) {
-            case 1: return (step_fn)k_step_warp<2, DRL_QMAX, D943>;
-            case 2: return (step_fn)k_step_warp<1, DRL_QMAX, D833>;
-            default: return e->nb == 1 ? step_warp_q<1, DynDims>(e->envs_per_warp) : step_warp_q<2, DynDims>(e->envs_per_warp);
+            case 1: return (const void*)k_step_warp<2, DRL_QMAX, D943>;
+            case 2: return (const void*)k_step_warp<1, DRL_QMAX, D833>;
+            default: return (const void*)(e->nb == 1 ? step_warp_q<1, DynDims>(e->envs_per_warp) : step_warp_q<2, DynDims>(e->envs_per_warp));
         }
     }
-    if (static_shape(e) == 3) return (step_fn)k_step_cta<(64 * 64 / 2) / kCtaThreads, DLW>;
-    return e->nb == 2 ? (step_fn)k_step_cta<2, DynDims> : e->nb == 4 ? (step_fn)k_step_cta<4, DynDims>
-         : e->nb == 8 ? (step_fn)k_step_cta<8, DynDims> : (step_fn)k_step_cta<16, DynDims>;
+    if (static_shape(e) == 3) return (const void*)k_step_cta<(64 * 64 / 2) / kCtaThreads, DLW>;
+    return e->nb == 2 ? (const void*)k_step_cta<2, DynDims> : e->nb == 4 ? (const void*)k_step_cta<4, DynDims>
+         : e->nb == 8 ? (const void*)k_step_cta<8, DynDims> : (const void*)k_step_cta<16, DynDims>;
+}
+// Fast CTA-mode kernel of this shape (nullptr: none -- warp mode, or switched off with DRL_NO_FAST=1 for A/B runs).
+static int fast_nb(const drl_env* e) {
+    const int H = e->dc.H;
+    return H <= 2 * kFastThreads ? 2 : H <= 4 * kFastThreads ? 4 : H <= 8 * kFastThreads ? 8 : H <= 16 * kFastThreads ? 16 : 0;
+}
+static const void* pick_fast(const drl_env* e) {
+    if (e->warp_mode || !e->use_fast) return nullptr;
+    if (static_shape(e) == 3) return (const void*)k_step_fast<(64 * 64 / 2) / kFastThreads, DLW>;
+    switch (fast_nb(e)) {
+        case 2: return (const void*)k_step_fast<2, DynDims>;
+        case 4: return (const void*)k_step_fast<4, DynDims>;
+        case 8: return (const void*)k_step_fast<8, DynDims>;
+        case 16: return (const void*)k_step_fast<16, DynDims>;
+        default: return nullptr;
+    }
 }
 static reset_fn pick_reset(const drl_env* e) {
     if (e->warp_mode) return e->nb == 1 ? (reset_fn)k_reset_warp<1> : (reset_fn)k_reset_warp<2>;
@@ -369,7 +486,7 @@ static int configure_launches(drl_env* e) {
     const DevCfg& c = e->dc;
     const int Q = e->envs_per_warp;
     const int threads = e->warp_mode ? kWarpsPerBlock * 32 : kCtaThreads;
-    const void* fns[3] = {(const void*)pick_step(e), (const void*)pick_reset(e), (const void*)pick_obs(e)};
+    const void* fns[3] = {pick_step(e), (const void*)pick_reset(e), (const void*)pick_obs(e)};
     int* grids[3] = {&e->grid_step, &e->grid_reset, &e->grid_obs};
     for (int i = 0; i < 3; ++i) {
         const long long per_cta = e->warp_mode ? (long long)kWarpsPerBlock * (i == 0 ? Q : 1) : 1;
@@ -386,7 +503,62 @@ static int configure_launches(drl_env* e) {
         *grids[i] = (int)(units < resident ? units : resident);
         if (i == 0) e->per_sm_step = per_sm;
     }
+    e->per_sm_fast = 0;
+    if (const void* ff = pick_fast(e)) {
+        cudaError_t ce = cudaFuncSetAttribute(ff, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem_optin);
+        int per_sm = 0;
+        if (ce == cudaSuccess) ce = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ff, kFastThreads, e->fast_dc.group_bytes);
+        if (ce != cudaSuccess || per_sm < 1)
+            return fail(e, DRL_ECUDA, "kernel %s setup failed (CUDA error %lld, blocks/SM %lld)", "fast step", (long long)ce,
+                        (long long)per_sm);
+        e->per_sm_fast = per_sm;
+    }
     return DRL_OK;
+}
+
+// One step of the env range [first, first + count) of the bound state: the warp kernel, or in CTA mode the fast
+// kernel followed by the general kernel on the fast kernel's redo list (``slot`` < 16 names the list header, so
+// launches that overlap on different streams use different ones).  Returns DRL_OK and adds the kernels launched
+// to *launches.
+static int launch_step(drl_env* env, long long first, long long count, const uint32_t* d_keys, const int8_t* d_actions,
+                       float* d_rewards, uint8_t* d_dones, float* d_obs, cudaStream_t s, int slot, int* launches) {
+    DevCfg dc = env->dc;
+    dc.N = count;
+    const long long n = dc.n;
+    uint8_t* ground = env->d_ground + first * dc.GS;
+    uint32_t* drones = env->d_drones + first * n;
+    const uint32_t* keys = d_keys + 2 * first;
+    const int8_t* actions = d_actions + first * n;
+    float* rewards = d_rewards + first * n;
+    uint8_t* dones = d_dones + first * n;
+    float* obs = d_obs ? d_obs + first * dc.obs_n * dc.W2 * 6 : nullptr;
+    if (env->warp_mode) {
+        const long long per_cta = (long long)kWarpsPerBlock * env->envs_per_warp;
+        const long long units = (count + per_cta - 1) / per_cta, resident = (long long)env->per_sm_step * env->sm_count;
+        if (launches) *launches += 1;
+        return launch(env, "step kernel", pick_step(env), (int)(units < resident ? units : resident), kWarpsPerBlock * 32,
+                      env->smem_bytes, (void*)s, dc, ground, drones, keys, actions, rewards, dones, obs, env->d_stats);
+    }
+    const long long resident = (long long)env->per_sm_step * env->sm_count;
+    const int grid_slow = (int)(count < resident ? count : resident);
+    int* hdr = nullptr;
+    int* list = nullptr;
+    if (const void* ff = pick_fast(env)) {
+        hdr = env->d_redo + 4 * slot;
+        list = env->d_redo + 64 + first;
+        const long long rf = (long long)env->per_sm_fast * env->sm_count;
+        DevCfg fdc = env->fast_dc;
+        fdc.N = count;
+        fdc.obs_n = dc.obs_n;
+        fdc.ntiles = dc.ntiles;
+        int rc = launch(env, "fast step kernel", ff, (int)(count < rf ? count : rf), kFastThreads, fdc.group_bytes, (void*)s, fdc,
+                        ground, drones, keys, actions, rewards, dones, obs, env->d_stats, hdr, list);
+        if (rc) return rc;
+        if (launches) *launches += 1;
+    }
+    if (launches) *launches += 1;
+    return launch(env, "step kernel", pick_step(env), grid_slow, kCtaThreads, env->smem_bytes, (void*)s, dc, ground, drones, keys,
+                  actions, rewards, dones, obs, env->d_stats, hdr, (const int*)list);
 }
 
 extern "C" {
@@ -470,27 +642,12 @@ int drl_create(const drl_config* cfg, drl_env** out) {
     c.tile_bufs = 1;
     e->envs_per_warp = !e->warp_mode ? 1 : n <= 4 ? DRL_QMAX : n <= 8 ? 4 : n <= 16 ? 2 : 1;
     const int Q = e->envs_per_warp;
-    c.off_code = (e->warp_mode ? 2 : 1) * Q * c.GS;  // warp step kernel: two staging buffers of Q ground rows
-    c.off_sdr = c.off_code + Q * round_up((int)G2, 16);
-    c.off_sdf = c.off_sdr + 128;
-    c.off_misc = c.off_sdf + 128;
-    c.off_rec = c.off_misc + 32;                    // [2][32] staged drone records
-    c.off_key = c.off_rec + 256;                    // [2][Q][2] staged keys
-    c.off_red = c.off_key + 64;
-    c.off_sel = round_up(c.off_red + 2 * (kCtaThreads / 32) * 8, 16);
     c.sel_maxj = c.k_spawn > n ? c.k_spawn : n;
     for (int i = 0; i < 4; ++i) c.sel_maxj = c.k_reset[i] > c.sel_maxj ? c.k_reset[i] : c.sel_maxj;
-    c.sel_cap = c.sel_maxj + 256;                   // J keys plus a generous few histogram bins' worth
-    // CTA mode only: histogram [256] + counters [4] | key list [cap] | rank -> position table [maxj]
-    const int sel_bytes = e->warp_mode ? 0 : 1040 + c.sel_cap * 8 + round_up(c.sel_maxj * 2, 16);
-    c.off_tile = round_up(c.off_sel + sel_bytes, 128);
-    if (e->warp_mode) {
-        c.group_bytes = c.off_tile + c.tile_bufs * c.tile_stride;
-        e->smem_bytes = c.group_bytes * kWarpsPerBlock;
-    } else {
-        c.group_bytes = c.off_tile + c.tile_bufs * c.tile_stride * (kCtaThreads / 32);
-        e->smem_bytes = c.group_bytes;
-    }
+    carve_layout(c, e->warp_mode, Q, false, kCtaThreads);
+    e->smem_bytes = e->warp_mode ? c.group_bytes * kWarpsPerBlock : c.group_bytes;
+    e->fast_dc = c;
+    if (!e->warp_mode) carve_layout(e->fast_dc, false, 1, true, kFastThreads);
     if (e->smem_bytes > (int)prop.sharedMemPerBlockOptin) {
         const long long need = e->smem_bytes;
         delete e;
@@ -499,6 +656,10 @@ int drl_create(const drl_config* cfg, drl_env** out) {
     }
 
     e->smem_optin = (int)prop.sharedMemPerBlockOptin;
+    {
+        const char* nf = getenv("DRL_NO_FAST");          // A/B switch: general CTA kernel only
+        e->use_fast = !e->warp_mode && !(nf && nf[0] == '1') && n <= 32;
+    }
     if (configure_launches(e) != DRL_OK) {
         snprintf(g_create_err, sizeof(g_create_err), "%s", e->err);
         delete e;
@@ -510,6 +671,14 @@ int drl_create(const drl_config* cfg, drl_env** out) {
         delete e;
         return fail(nullptr, DRL_ECUDA, "cudaMalloc of the statistics block failed%s");
     }
+    if (!e->warp_mode) {
+        const size_t bytes = (size_t)(c.N + 64) * sizeof(int);
+        if (cudaMalloc(&e->d_redo, bytes) != cudaSuccess || cudaMemset(e->d_redo, 0, bytes) != cudaSuccess) {
+            cudaFree(e->d_stats);
+            delete e;
+            return fail(nullptr, DRL_ECUDA, "cudaMalloc of the redo list failed%s");
+        }
+    }
     *out = e;
     return DRL_OK;
 }
@@ -518,6 +687,7 @@ void drl_destroy(drl_env* env) {
     if (!env) return;
     cudaSetDevice(env->cfg.device);
     cudaFree(env->d_stats);
+    cudaFree(env->d_redo);
     cudaFree(env->s_keys);
     cudaFree(env->s_actions);
     cudaFree(env->s_rewards);
@@ -648,10 +818,8 @@ int drl_step(drl_env* env, const void* d_keys, const void* d_actions, void* d_re
     if (!env->d_ground) return fail(env, DRL_ESTATE, "drl_step: state not bound (call drl_bind_state)%s");
     if ((uintptr_t)d_obs & 7) return fail(env, DRL_EINVAL, "drl_step: obs must be 8-byte aligned%s");
     CUDA_TRY(env, cudaSetDevice(env->cfg.device));
-    const int threads = env->warp_mode ? kWarpsPerBlock * 32 : kCtaThreads;
-    return launch(env, "step kernel", (const void*)pick_step(env), env->grid_step, threads, env->smem_bytes, stream, env->dc,
-                  env->d_ground, env->d_drones, (const uint32_t*)d_keys, (const int8_t*)d_actions, (float*)d_rewards,
-                  (uint8_t*)d_dones, (float*)d_obs, env->d_stats);
+    return launch_step(env, 0, env->dc.N, (const uint32_t*)d_keys, (const int8_t*)d_actions, (float*)d_rewards, (uint8_t*)d_dones,
+                       (float*)d_obs, (cudaStream_t)stream, 0, nullptr);
 }
 
 int drl_get_obs(drl_env* env, void* d_obs, void* stream) {
@@ -677,21 +845,6 @@ static int ensure_scratch(drl_env* env) {
     }
     CUDA_TRY(env, cudaEventCreateWithFlags(&env->pipe_begin, cudaEventDisableTiming));
     return DRL_OK;
-}
-
-// Step kernel over the env range [first, first + count) of the bound state (chunked launches).
-static int launch_step_range(drl_env* env, long long first, long long count, const uint32_t* d_keys, const int8_t* d_actions,
-                             float* d_rewards, uint8_t* d_dones, float* d_obs, cudaStream_t s) {
-    DevCfg dc = env->dc;
-    dc.N = count;
-    const long long n = dc.n;
-    const long long per_cta = env->warp_mode ? (long long)kWarpsPerBlock * env->envs_per_warp : 1;
-    const long long units = (count + per_cta - 1) / per_cta, resident = (long long)env->per_sm_step * env->sm_count;
-    const int threads = env->warp_mode ? kWarpsPerBlock * 32 : kCtaThreads;
-    float* obs = d_obs ? d_obs + first * dc.obs_n * dc.W2 * 6 : nullptr;
-    return launch(env, "step kernel", (const void*)pick_step(env), (int)(units < resident ? units : resident), threads,
-                  env->smem_bytes, (void*)s, dc, env->d_ground + first * dc.GS, env->d_drones + first * n, d_keys + 2 * first,
-                  d_actions + first * n, d_rewards + first * n, d_dones + first * n, obs, env->d_stats);
 }
 
 int drl_step_host(drl_env* env, const uint32_t key[2], const int8_t* h_actions, float* h_rewards, uint8_t* h_dones,
@@ -721,7 +874,8 @@ int drl_step_host(drl_env* env, const uint32_t key[2], const int8_t* h_actions, 
         cudaStream_t ps = env->pipe_stream[used & 1];
         if (used < 2) CUDA_TRY(env, cudaStreamWaitEvent(ps, env->pipe_begin, 0));
         CUDA_TRY(env, cudaMemcpyAsync(env->s_actions + first * n, h_actions + first * n, count * n, cudaMemcpyHostToDevice, ps));
-        rc = launch_step_range(env, first, count, env->s_keys, env->s_actions, env->s_rewards, env->s_dones, (float*)d_obs, ps);
+        rc = launch_step(env, first, count, env->s_keys, env->s_actions, env->s_rewards, env->s_dones, (float*)d_obs, ps, 1 + used,
+                         nullptr);
         if (rc) return rc;
         CUDA_TRY(env, cudaMemcpyAsync(h_rewards + first * n, env->s_rewards + first * n, count * n * 4, cudaMemcpyDeviceToHost, ps));
         CUDA_TRY(env, cudaMemcpyAsync(h_dones + first * n, env->s_dones + first * n, count * n, cudaMemcpyDeviceToHost, ps));
@@ -753,7 +907,7 @@ int drl_rollout_random(drl_env* env, uint32_t rng[2], int32_t steps, int32_t res
         if (rc) return rc;
         rc = drl_step(env, d_keys, d_actions, d_rewards, d_dones, d_obs, stream);   // :54-55
         if (rc) return rc;
-        launches += 3;
+        launches += 2 + (pick_fast(env) ? 2 : 1);     // randint, key split, step (fast + general kernel in CTA mode)
         drl_split2(rng, nk, sub);                                  // rng, key = split(rng)   :82 (the trainer's batch key)
         rng[0] = nk[0]; rng[1] = nk[1];
         if (reset_every > 0 && (step0 + t) % reset_every == 0) {   // :101-113 (resets with the carried rng itself)

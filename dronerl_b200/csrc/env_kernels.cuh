@@ -56,8 +56,8 @@ struct DevCfg {
     int tile_stride;           // bytes reserved per obs tile buffer
     int tile_bufs;             // tile buffers per warp (1, or 2 alternating)
     // shared-memory carve-up (bytes from the group's base)
-    int off_code, off_sdr, off_sdf, off_misc, off_rec, off_key, off_red, off_sel, off_tile;
-    int sel_cap, sel_maxj;     // CTA mode: capacity of the selection list, of the rank -> position table
+    int off_code, off_sdr, off_sdf, off_misc, off_red, off_sel, off_tile;
+    int sel_hist, sel_cap, sel_maxj;   // CTA mode: bytes of histogram, capacity of the key list, of the rank -> position table
     int group_bytes;           // warp mode: bytes per warp; CTA mode: bytes per CTA
     long long N;               // local envs
 };
@@ -230,16 +230,22 @@ __device__ __forceinline__ uint32_t slot_mask(const uint8_t* arr, int tid, const
 // mant[s] = 23-bit mantissa of jax.random.uniform(key, (G*G,))[cell(s)]  (env.py:54,78)
 template <int T, int NB, class D>
 __device__ __forceinline__ void noise_mantissas(int tid, const D& d, uint32_t k0, uint32_t k1, uint32_t (&mant)[2 * NB]) {
+    // every thread hashes its NB blocks together (interleaved rounds); blocks past the end of the vector hash
+    // a harmless counter and are discarded (their slots are not in valid_slots() either)
+    uint32_t x0[NB], x1[NB];
 #pragma unroll
     for (int t = 0; t < NB; ++t) {
         const int b = slot_block<T, NB>(tid, t);
-        uint32_t o0 = 0, o1 = 0;
-        if (b < d.H()) {
-            const int hi = d.H() + b;
-            drl_threefry2x32(k0, k1, (uint32_t)b, hi < d.G2() ? (uint32_t)hi : 0u, o0, o1);
-        }
-        mant[2 * t] = o0 >> 9;
-        mant[2 * t + 1] = o1 >> 9;
+        const int hi = d.H() + b;
+        x0[t] = (uint32_t)b;
+        x1[t] = hi < d.G2() ? (uint32_t)hi : 0u;      // odd sizes: the pad counter is zero
+    }
+    drl_threefry2x32_n<NB>(k0, k1, x0, x1);
+#pragma unroll
+    for (int t = 0; t < NB; ++t) {
+        const bool in = slot_block<T, NB>(tid, t) < d.H();
+        mant[2 * t] = in ? x0[t] >> 9 : 0u;
+        mant[2 * t + 1] = in ? x1[t] >> 9 : 0u;
     }
 }
 
@@ -318,9 +324,9 @@ struct Sel {
 __device__ __forceinline__ Sel carve_sel(unsigned char* base, const DevCfg& c) {
     Sel s;
     s.hist = reinterpret_cast<uint32_t*>(base + c.off_sel);
-    s.cnt = s.hist + 256;
-    s.list = reinterpret_cast<unsigned long long*>(base + c.off_sel + 1040);
-    s.pos = reinterpret_cast<uint16_t*>(base + c.off_sel + 1040 + (size_t)c.sel_cap * 8);
+    s.cnt = reinterpret_cast<uint32_t*>(base + c.off_sel + c.sel_hist);
+    s.list = reinterpret_cast<unsigned long long*>(base + c.off_sel + c.sel_hist + 16);
+    s.pos = reinterpret_cast<uint16_t*>(base + c.off_sel + c.sel_hist + 16 + (size_t)c.sel_cap * 8);
     s.cap = c.sel_cap;
     return s;
 }
@@ -642,39 +648,22 @@ __device__ __forceinline__ void obs_tiles(const D& d, const DevCfg& c, const Sme
     }
 }
 
-// ---- one env step on the state staged in shared memory ---------------------------------------
-//
-// Preconditions: sm.sg holds the env's ground, sm.code is all zero, group is synchronised;
-// ``validm`` = valid_slots() of this thread, ``F0`` = number of free (zero) cells of that ground.
-// Drone i lives in lane i of warp 0 of the group (``rec``/``act`` valid there).
-// Postconditions: sm.sg holds the new ground, ``rec`` the new drone record, rewards/dones written.
-template <int T, int NB, class D>
-__device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const D& d, const Smem& sm, const Sel& sel, uint32_t validm, int F0,
-                                         uint32_t& rec, int act, uint32_t k0, uint32_t k1, float* rewards_e,
-                                         uint8_t* dones_e, Stats& st) {
-    constexpr bool kWarp = Group<T>::kWarp;
-    const int tid = Group<T>::tid();
-    const int lane = threadIdx.x & 31;
-    const bool drone_warp = kWarp || threadIdx.x < 32;
-    const int G = d.G(), G2 = d.G2(), n = d.n();
-
-    // Which owned cells held a skyscraper BEFORE the step (spawn_air's exclude mask).  Skyscrapers only
-    // ever change when a spawn runs out of free cells (the erasing-zeros edge), so the mask is captured
-    // lazily: right before such an edge, or else at respawn time from the unchanged cells.
-    uint32_t oldsky = 0;
-    bool have_oldsky = false;
-    auto capture_oldsky = [&]() {
-        if (!have_oldsky) {
-            oldsky = slot_mask<T, NB>(sm.sg, tid, d, validm, [](uint32_t v) { return v == (uint32_t)SKY; });
-            have_oldsky = true;
-        }
-    };
-
-    uint32_t mP = 0, mD = 0, mDone = 0;
-    int x = 0, y = 0, carry = 0, ch = 0, tcell = 0, npick = 0;
+// Per-drone part of a step for the drones of one env living in the lanes of one warp (env.py:145-194,215-219).
+struct DroneOut {
+    uint32_t mP = 0, mD = 0, mDone = 0;     // masks: packet respawn, delivered, done
+    int x = 0, y = 0, carry = 0, ch = 0, tcell = 0, npick = 0, ndel = 0;
     bool done = false, surv = false, del_clear = false;
+};
 
-    if (drone_warp) {
+template <class D>
+__device__ __forceinline__ DroneOut drone_phase(const DevCfg& c, const D& d, const Smem& sm, int lane, uint32_t rec, int act,
+                                                float* rewards_e, uint8_t* dones_e, Stats& st) {
+    const int G = d.G(), n = d.n();
+    DroneOut o;
+    int x, y, carry, ch, tcell;
+    bool done, surv, del_clear;
+    uint32_t mP, mD, mDone;
+    {
         const bool isd = lane < n;
         x = rec & 0xFFu; y = (rec >> 8) & 0xFFu;
         const bool carry_old = (rec >> 16) & 1u;
@@ -728,7 +717,52 @@ __device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const D
             st.dones += done; st.crashes += collided; st.pickups += picked; st.deliveries += delivered;
             st.charging += charging;
         }
-        npick = __popc(__ballot_sync(FULL, pick_clear));
+        o.npick = __popc(__ballot_sync(FULL, pick_clear));
+        o.ndel = __popc(__ballot_sync(FULL, del_clear));
+    }
+    o.mP = mP; o.mD = mD; o.mDone = mDone;
+    o.x = x; o.y = y; o.carry = carry; o.ch = ch; o.tcell = tcell;
+    o.done = done; o.surv = surv; o.del_clear = del_clear;
+    return o;
+}
+
+// ---- one env step on the state staged in shared memory ---------------------------------------
+//
+// Preconditions: sm.sg holds the env's ground, sm.code is all zero, group is synchronised;
+// ``validm`` = valid_slots() of this thread, ``F0`` = number of free (zero) cells of that ground.
+// Drone i lives in lane i of warp 0 of the group (``rec``/``act`` valid there).
+// Postconditions: sm.sg holds the new ground, ``rec`` the new drone record, rewards/dones written.
+template <int T, int NB, class D>
+__device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const D& d, const Smem& sm, const Sel& sel, uint32_t validm, int F0,
+                                         uint32_t& rec, int act, uint32_t k0, uint32_t k1, float* rewards_e,
+                                         uint8_t* dones_e, Stats& st) {
+    constexpr bool kWarp = Group<T>::kWarp;
+    const int tid = Group<T>::tid();
+    const int lane = threadIdx.x & 31;
+    const bool drone_warp = kWarp || threadIdx.x < 32;
+    const int G = d.G(), G2 = d.G2(), n = d.n();
+
+    // Which owned cells held a skyscraper BEFORE the step (spawn_air's exclude mask).  Skyscrapers only
+    // ever change when a spawn runs out of free cells (the erasing-zeros edge), so the mask is captured
+    // lazily: right before such an edge, or else at respawn time from the unchanged cells.
+    uint32_t oldsky = 0;
+    bool have_oldsky = false;
+    auto capture_oldsky = [&]() {
+        if (!have_oldsky) {
+            oldsky = slot_mask<T, NB>(sm.sg, tid, d, validm, [](uint32_t v) { return v == (uint32_t)SKY; });
+            have_oldsky = true;
+        }
+    };
+
+    uint32_t mP = 0, mD = 0, mDone = 0;
+    int x = 0, y = 0, carry = 0, ch = 0, tcell = 0, npick = 0;
+    bool done = false, surv = false, del_clear = false;
+
+    if (drone_warp) {
+        const DroneOut o = drone_phase(c, d, sm, lane, rec, act, rewards_e, dones_e, st);
+        mP = o.mP; mD = o.mD; mDone = o.mDone; npick = o.npick;
+        x = o.x; y = o.y; carry = o.carry; ch = o.ch; tcell = o.tcell;
+        done = o.done; surv = o.surv; del_clear = o.del_clear;
         if (!kWarp && lane == 0) { sm.misc[0] = mP; sm.misc[1] = mD; sm.misc[2] = mDone; sm.misc[3] = (uint32_t)npick; }
     }
     if (!kWarp) {
@@ -807,6 +841,144 @@ __device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const D
     if (drone_warp)
         rec = (uint32_t)x | ((uint32_t)y << 8) | ((uint32_t)carry << 16) | ((uint32_t)ch << 24);
     Group<T>::sync();
+}
+
+// ---- CTA mode, fast path: streamed selection --------------------------------------------------------
+//
+// The general step above keeps a whole noise vector in registers (2 NB mantissas per thread) because the
+// rare cases need it: ranks that run into the -inf tail, the erasing-zeros edge, list overflow.  The common
+// case needs none of that: the J <= 32 winners are the candidates among the few dozen largest mantissas, so
+// every block is hashed, compared against the pre-filter threshold and dropped -- nothing is kept per thread,
+// the register budget shrinks and more CTAs fit an SM.  Whenever the fast path cannot prove its result
+// (too few or too many survivors, an erasing edge) it reports failure, nothing of the env is written back
+// and the env is stepped again by the general kernel from its untouched state (redo list).
+template <int T, int NB, class D, class P>
+__device__ __forceinline__ bool stream_select(Group<T>& grp, const D& d, const Sel& sel, int tid, uint32_t k0, uint32_t k1,
+                                              int J, int ncand, P&& pred) {
+    constexpr int CH = NB < 4 ? NB : 4;                     // blocks hashed together (interleaved rounds)
+    static_assert(NB % CH == 0, "NB must be 1, 2 or a multiple of 4");
+    int sq = 1;
+    while (sq * sq < J) ++sq;
+    const int target = J + 4 * sq + 8;                      // <= 64 for J <= 32
+    uint32_t T0 = 0;
+    if (ncand > target) T0 = (uint32_t)(8388608.0f * (1.0f - __fdividef((float)target, (float)ncand)));
+    const uint32_t T0s = T0 << 9;                           // (o >> 9) >= T0  <=>  o >= T0 << 9
+    uint32_t* const counter = sel.cnt + 1 + grp.spar;       // see rank_positions: two alternating counters
+    if (tid == 0) sel.cnt[1 + (grp.spar ^ 1)] = 0u;
+    grp.spar ^= 1;
+    const int H = d.H(), G2 = d.G2();
+    auto push = [&](uint32_t o, int cell) {
+        const uint32_t i = atomicAdd(counter, 1u);
+        if (i < 128u) sel.list[i] = ((unsigned long long)((o >> 9) + 1u) << 16) | (unsigned)(G2 - cell);
+    };
+#pragma unroll 1
+    for (int c0 = 0; c0 < NB; c0 += CH) {
+        uint32_t x0[CH], x1[CH];
+        const int b0 = tid * NB + c0;
+#pragma unroll
+        for (int t = 0; t < CH; ++t) {
+            const int hi = H + b0 + t;
+            x0[t] = (uint32_t)(b0 + t);
+            x1[t] = hi < G2 ? (uint32_t)hi : 0u;
+        }
+        drl_threefry2x32_n<CH>(k0, k1, x0, x1);
+#pragma unroll
+        for (int t = 0; t < CH; ++t) {
+            const int b = b0 + t;
+            if (x0[t] >= T0s && b < H && pred(b)) push(x0[t], b);
+            if (x1[t] >= T0s && b < H && H + b < G2 && pred(H + b)) push(x1[t], H + b);
+        }
+    }
+    __syncthreads();
+    const int m = (int)*counter;
+    if (m < J || m > 128) return false;                     // uniform over the CTA
+    for (int base = 0; base < m; base += T / 4) {           // rank by counting, four threads per key
+        const int kq = base + (tid >> 2);
+        const bool live = kq < m;
+        const unsigned long long key = live ? sel.list[kq] : 0ull;
+        int r = 0;
+        if (live)
+            for (int u = tid & 3; u < m; u += 4) r += sel.list[u] > key;
+        r += __shfl_xor_sync(FULL, r, 1);
+        r += __shfl_xor_sync(FULL, r, 2);
+        if (live && (tid & 3) == 0 && r < J) sel.pos[r] = (uint16_t)(G2 - (int)(key & 0xFFFFull));
+    }
+    __syncthreads();
+    return true;
+}
+
+// One env step, fast path.  Same contract as env_step, plus: ``F0`` and the staged ground come from the caller,
+// returns false (uniformly) when the env has to be redone by the general kernel; shared state is then garbage
+// except that sm.code is all zero again.  rewards/dones are written either way (the redo writes the same).
+template <int T, int NB, class D>
+__device__ __forceinline__ bool env_step_fast(Group<T>& grp, const DevCfg& c, const D& d, const Smem& sm, const Sel& sel, int F0,
+                                              uint32_t& rec, int act, uint32_t k0, uint32_t k1, float* rewards_e,
+                                              uint8_t* dones_e, Stats& st) {
+    const int tid = threadIdx.x, lane = threadIdx.x & 31;
+    const bool drone_warp = threadIdx.x < 32;
+    const int G = d.G(), G2 = d.G2(), n = d.n();
+    DroneOut o;
+    if (drone_warp) {
+        o = drone_phase(c, d, sm, lane, rec, act, rewards_e, dones_e, st);
+        if (lane == 0) {
+            sm.misc[0] = o.mP; sm.misc[1] = o.mD; sm.misc[2] = o.mDone;
+            sm.misc[3] = (uint32_t)o.npick | ((uint32_t)o.ndel << 16);
+        }
+    }
+    __syncthreads();                                        // also: pickup clears are visible
+    const uint32_t mP = sm.misc[0], mD = sm.misc[1], mDone = sm.misc[2];
+    const int npick = (int)(sm.misc[3] & 0xFFFFu), ndel = (int)(sm.misc[3] >> 16);
+    const int k = c.k_spawn;
+    const int F1 = F0 + npick;                              // free cells after the pickups
+    const int F2 = F1 - __popc(mP) + ndel;                  // ... after the packet respawn and the delivery clears
+    // the erasing-zeros edges (a fill vector longer than the free cells) belong to the general kernel
+    if (F1 < k || F2 < k) return false;
+    uint32_t sk0 = 0, sk1 = 0;
+    if (mP != 0 || mD != 0 || mDone != 0) split_warp(k0, k1, sk0, sk1);          // key, spawn_key = split(key)
+    auto is_free = [&](int cell) { return sm.sg[cell] == 0; };
+    // S8 packet respawn (env.py:197-203)
+    if (mP != 0) {
+        const int J = 32 - __clz(mP);
+        if (!stream_select<T, NB>(grp, d, sel, tid, sk0, sk1, J, F1, is_free)) return false;
+        for (int j = tid; j < J; j += T) sm.sg[sel.pos[j]] = ((mP >> j) & 1u) ? PACKET : 0;
+    }
+    // S9 dropzone respawn (env.py:205-212): same spawn_key, the noise is hashed again (deliveries are rare)
+    if (mD != 0) {
+        __syncthreads();                                    // mask zeroing comes after the packet spawn's writes
+        if (drone_warp && o.del_clear) sm.sg[o.tcell] = 0;
+        __syncthreads();
+        const int J = 32 - __clz(mD);
+        if (!stream_select<T, NB>(grp, d, sel, tid, sk0, sk1, J, F2, is_free)) return false;
+        for (int j = tid; j < J; j += T) sm.sg[sel.pos[j]] = ((mD >> j) & 1u) ? DROPZONE : 0;
+    }
+    // S11 respawn of done drones (env.py:222-230) and S12 pickup on respawn (env.py:233-241)
+    int x = o.x, y = o.y, carry = o.carry;
+    if (mDone != 0) {
+        split_warp(k0, k1, sk0, sk1);                       // key, spawn_key = split(key)  (second split)
+        // p_choice[x, y] = False for survivors (row = x): a bitmap here, one bit per cell
+        uint32_t* const sbits = reinterpret_cast<uint32_t*>(sm.code);
+        if (drone_warp && o.surv) atomicOr(&sbits[(x * G + y) >> 5], 1u << ((x * G + y) & 31));
+        __syncthreads();                                    // also orders the ground writes above
+        // no erasing edge on this path, so the skyscrapers are those of the old ground
+        auto is_cand = [&](int cell) { return !((sbits[cell >> 5] >> (cell & 31)) & 1u) && sm.sg[cell] != SKY && cell != G2 - 1; };
+        const int J = 32 - __clz(mDone);
+        const bool ok = stream_select<T, NB>(grp, d, sel, tid, sk0, sk1, J, G2 - 1 - c.k_reset[3] - n, is_cand);
+        if (drone_warp && o.surv) sbits[(x * G + y) >> 5] = 0u;   // restore the all-zero invariant
+        if (!ok) return false;
+        if (drone_warp && o.done) {
+            const int pos = sel.pos[lane];
+            x = (int)d.divG((uint32_t)pos);                 // rank i -> drone i: x = pos // G, y = pos % G
+            y = pos - x * G;
+            if (sm.sg[pos] == PACKET) {                     // package_mask[new_x, new_y]: flat index x*G+y == pos
+                carry = 1;
+                sm.sg[pos] = 0;
+                st.respawn_pickups += 1;
+            }
+        }
+    }
+    if (drone_warp) rec = (uint32_t)x | ((uint32_t)y << 8) | ((uint32_t)carry << 16) | ((uint32_t)o.ch << 24);
+    __syncthreads();
+    return true;
 }
 
 // ---- one env reset (env.py:89-135) -------------------------------------------------------------

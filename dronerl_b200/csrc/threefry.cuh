@@ -46,6 +46,40 @@ DRL_HD void drl_threefry2x32(uint32_t k0, uint32_t k1, uint32_t c0, uint32_t c1,
     o1 = x1;
 }
 
+// NB independent blocks under one key, rounds interleaved across the blocks: one block is a chain of 60+
+// dependent integer instructions, so hashing the blocks one after the other leaves the ALU latency exposed
+// (ncu: "wait" was the top stall of the step kernels); interleaved, NB chains are in flight per thread.
+#if defined(__CUDACC__)
+#define DRL_TF_ROUND_N(r)                      \
+    _Pragma("unroll") for (int t = 0; t < NB; ++t) { \
+        x0[t] += x1[t];                        \
+        x1[t] = drl_rotl32(x1[t], (r));        \
+        x1[t] ^= x0[t];                        \
+    }
+#define DRL_TF_INJECT_N(ka, kb, i)             \
+    _Pragma("unroll") for (int t = 0; t < NB; ++t) { \
+        x0[t] += (ka);                         \
+        x1[t] += (kb) + (i);                   \
+    }
+template <int NB>
+__device__ __forceinline__ void drl_threefry2x32_n(uint32_t k0, uint32_t k1, uint32_t (&x0)[NB], uint32_t (&x1)[NB]) {
+    // in: x0[t], x1[t] = the two counter words of block t; out: the two output words
+    const uint32_t k2 = k0 ^ k1 ^ 0x1BD11BDAu;
+#pragma unroll
+    for (int t = 0; t < NB; ++t) { x0[t] += k0; x1[t] += k1; }
+    DRL_TF_ROUND_N(13) DRL_TF_ROUND_N(15) DRL_TF_ROUND_N(26) DRL_TF_ROUND_N(6)
+    DRL_TF_INJECT_N(k1, k2, 1u)
+    DRL_TF_ROUND_N(17) DRL_TF_ROUND_N(29) DRL_TF_ROUND_N(16) DRL_TF_ROUND_N(24)
+    DRL_TF_INJECT_N(k2, k0, 2u)
+    DRL_TF_ROUND_N(13) DRL_TF_ROUND_N(15) DRL_TF_ROUND_N(26) DRL_TF_ROUND_N(6)
+    DRL_TF_INJECT_N(k0, k1, 3u)
+    DRL_TF_ROUND_N(17) DRL_TF_ROUND_N(29) DRL_TF_ROUND_N(16) DRL_TF_ROUND_N(24)
+    DRL_TF_INJECT_N(k1, k2, 4u)
+    DRL_TF_ROUND_N(13) DRL_TF_ROUND_N(15) DRL_TF_ROUND_N(26) DRL_TF_ROUND_N(6)
+    DRL_TF_INJECT_N(k2, k0, 5u)
+}
+#endif
+
 // Element ``f`` of jax.random.bits(key, (size,)) in the original counter layout:
 // counters iota(size) (+ one ZERO pad when size is odd) are split in halves that
 // form the two words of each block; word-0 outputs come first, then word-1 outputs.

@@ -22,6 +22,9 @@ CONFIGS = [
     (4, 2, 2, {'packets_factor': 4, 'dropzones_factor': 2, 'stations_factor': 1, 'skyscrapers_factor': 1}, 2048, 80),   # free < k edge: top_k runs into occupied cells
     (3, 3, 1, {'packets_factor': 1, 'dropzones_factor': 1, 'stations_factor': 0, 'skyscrapers_factor': 1}, 2048, 60),   # tiny: spawn_air runs out of candidates
     (32, 16, 3, {}, 128, 30),
+    (12, 6, 2, {'packets_factor': 8}, 512, 60),   # CTA mode, free cells hover around k: fast kernel and redo list interleave
+    (12, 6, 2, {'packets_factor': 10}, 512, 40),  # CTA mode, free < k on every step: every env goes through the redo list
+    (20, 32, 2, {'packets_factor': 1, 'dropzones_factor': 1, 'stations_factor': 1, 'skyscrapers_factor': 1}, 256, 40),   # 32 drones on a small CTA-mode grid
     (64, 32, 5, {'stations_factor': 8, 'skyscrapers_factor': 16}, 24, 12),   # BASELINE large world
 ]
 
