@@ -199,13 +199,20 @@ k_step_fast(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint
     Group<T> grp{reinterpret_cast<unsigned long long*>(smem_raw + c.off_red)};
     const Sel sel = carve_sel(smem_raw, c);
     zero_code(c, sm, threadIdx.x, T);
-    if (threadIdx.x == 0) sel.cnt[1] = sel.cnt[2] = 0u;
+    if (threadIdx.x == 0) sel.cnt[1] = sel.cnt[2] = sel.cnt[3] = 0u;
     Stats st;
     unsigned env_steps = 0;
     const D d{c};
     const int GS = d.GS(), nvec = GS >> 4, n = d.n();
     __syncthreads();
     for (long long e = blockIdx.x; e < c.N; e += gridDim.x) {
+        if (e + gridDim.x < c.N) {          // pull the next env's inputs into L2 while this one is stepped
+            const long long en = e + gridDim.x;
+            for (int i = threadIdx.x; i < nvec; i += T) asm volatile("prefetch.global.L2 [%0];" ::"l"(ground + en * GS + 16 * i));
+            if ((int)threadIdx.x < n) asm volatile("prefetch.global.L2 [%0];" ::"l"(drones + en * n + threadIdx.x));
+            if (threadIdx.x == 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(actions + en * n));
+            if (threadIdx.x == 33) asm volatile("prefetch.global.L2 [%0];" ::"l"(keys + 2 * en));
+        }
         int zc = 0;
         for (int i = threadIdx.x; i < nvec; i += T) {
             const uint4 v = reinterpret_cast<const uint4*>(ground + e * GS)[i];
@@ -389,7 +396,7 @@ static void carve_layout(DevCfg& c, bool warp_mode, int Q, bool fast, int cta_th
     c.off_red = c.off_misc + 32;
     c.off_sel = round_up(c.off_red + (warp_mode ? 0 : 2 * (cta_threads / 32) * 8), 16);
     c.sel_hist = fast ? 0 : 1024;
-    c.sel_cap = fast ? 128 : c.sel_maxj + 256;      // J keys plus a generous few histogram bins' worth
+    c.sel_cap = fast ? 384 : c.sel_maxj + 256;      // J keys plus a generous few histogram bins' worth (fast: 128 keys + 256 parked)
     // CTA mode only: histogram [256] | counters [4] | key list [cap] | rank -> position table [maxj]
     const int sel_bytes = warp_mode ? 0 : c.sel_hist + 16 + c.sel_cap * 8 + round_up(c.sel_maxj * 2, 16);
     c.off_tile = round_up(c.off_sel + sel_bytes, 128);

@@ -560,11 +560,48 @@ __device__ __forceinline__ void compose_tile(const D& d, const Smem& sm, int d0,
     // release the buffer: up to two rows per lane with ten 3-bit codes each in 32-bit registers, or one row
     // per lane with up to 21 codes in a 64-bit pair (radius-5 windows of the large world).
     const int cpi = (W + lpr - 1) / lpr;                    // cells per item
-    const bool packed32 = items <= 64 && cpi <= 10;
-    const bool packed64 = !packed32 && items <= 32 && cpi <= 21;
+    // Big grids (CTA mode), one window row of up to 12 cells per lane: most windows lie inside the grid, so the
+    // row is W contiguous ground bytes -- four aligned 32-bit loads, a funnel shift to the row's first byte, and
+    // one PRMT table lookup per word turn them into W channel bytes; rows that cross the left/right edge take the
+    // cell loop, rows above/below the grid are all wall.
+    const bool words = G * G > 128 && lpr == 1 && W <= 12 && items <= 32;
+    const bool packed32 = !words && items <= 64 && cpi <= 10;
+    const bool packed64 = !words && !packed32 && items <= 32 && cpi <= 21;
     uint32_t p0 = 0, p1 = 0;
     unsigned long long pw = 0;
-    if (packed32) {
+    uint32_t cw0 = 0, cw1 = 0, cw2 = 0;
+    if (words) {
+        if (lane < items) {
+            const int dd = (int)d.divW((uint32_t)lane);
+            const int wy = lane - dd * W;
+            const uint32_t rec = sm.sdr[d0 + dd];
+            const int gy = (int)((rec >> 8) & 0xFFu) + wy - d.r();
+            const int gx0 = (int)(rec & 0xFFu) - d.r();
+            if ((unsigned)gy >= (unsigned)G) {
+                cw0 = cw1 = cw2 = 0x05050505u;
+            } else if (gx0 >= 0 && gx0 + W <= G) {
+                const int base = gy * G + gx0;
+                const uint32_t* wp = reinterpret_cast<const uint32_t*>(sm.sg + (base & ~3));
+                const uint32_t sh = (uint32_t)(base & 3) * 8u;
+                const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2], w3 = wp[3];
+                auto lut4 = [&](uint32_t a) {               // four ground bytes -> four channel bytes
+                    const uint32_t t = a | (a >> 4);        // nibbles: byte 0 = b0 | b1 << 4, byte 2 = b2 | b3 << 4
+                    return __byte_perm(kLutLo, kLutHi, (t & 0xFFu) | ((t >> 8) & 0xFF00u));
+                };
+                cw0 = lut4(__funnelshift_r(w0, w1, sh));
+                cw1 = lut4(__funnelshift_r(w1, w2, sh));
+                cw2 = lut4(__funnelshift_r(w2, w3, sh));
+            } else {
+                const uint8_t* grow = sm.sg + gy * G;
+                for (int wx = 0; wx < W; ++wx) {
+                    const int gx = gx0 + wx;
+                    const uint32_t g = (unsigned)gx < (unsigned)G ? grow[gx] : (uint32_t)SKY;
+                    const uint32_t code = __byte_perm(kLutLo, kLutHi, g) << (8 * (wx & 3));
+                    if (wx < 4) cw0 |= code; else if (wx < 8) cw1 |= code; else cw2 |= code;
+                }
+            }
+        }
+    } else if (packed32) {
         if (lane < items) p0 = row_codes(lane, 0u);
         if (lane + 32 < items) p1 = row_codes(lane + 32, 0u);
     } else if (packed64) {
@@ -575,7 +612,16 @@ __device__ __forceinline__ void compose_tile(const D& d, const Smem& sm, int d0,
     float4* t4 = reinterpret_cast<float4*>(tile);
     for (int i = lane; i < vecs; i += 32) t4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     __syncwarp();
-    if (packed32) {
+    if (words) {
+        if (lane < items) {
+            float* o = tile + lane * W * 6;
+            for (int wx = 0; wx < W; ++wx) {
+                const uint32_t w = wx < 4 ? cw0 : wx < 8 ? cw1 : cw2;
+                const uint32_t ch = (w >> (8 * (wx & 3))) & 0xFFu;
+                if (ch) o[wx * 6 + ch] = 1.0f;
+            }
+        }
+    } else if (packed32) {
         if (lane < items) row_emit(lane, p0);
         if (lane + 32 < items) row_emit(lane + 32, p1);
     } else if (packed64) {
@@ -867,9 +913,13 @@ __device__ __forceinline__ bool stream_select(Group<T>& grp, const D& d, const S
     if (tid == 0) sel.cnt[1 + (grp.spar ^ 1)] = 0u;
     grp.spar ^= 1;
     const int H = d.H(), G2 = d.G2();
-    auto push = [&](uint32_t o, int cell) {
-        const uint32_t i = atomicAdd(counter, 1u);
-        if (i < 128u) sel.list[i] = ((unsigned long long)((o >> 9) + 1u) << 16) | (unsigned)(G2 - cell);
+    // Pass 1: hash, compare, and park the rare survivors (raw word + cell) in the upper half of the list; the
+    // candidate test and the key come later, one survivor per thread, so the divergent part of the loop is short.
+    uint2* const stage = reinterpret_cast<uint2*>(sel.list + 128);
+    uint32_t* const nstage = sel.cnt + 3;
+    auto park = [&](uint32_t o, int cell) {
+        const uint32_t i = atomicAdd(nstage, 1u);
+        if (i < 256u) stage[i] = make_uint2(o, (uint32_t)cell);
     };
 #pragma unroll 1
     for (int c0 = 0; c0 < NB; c0 += CH) {
@@ -885,11 +935,27 @@ __device__ __forceinline__ bool stream_select(Group<T>& grp, const D& d, const S
 #pragma unroll
         for (int t = 0; t < CH; ++t) {
             const int b = b0 + t;
-            if (x0[t] >= T0s && b < H && pred(b)) push(x0[t], b);
-            if (x1[t] >= T0s && b < H && H + b < G2 && pred(H + b)) push(x1[t], H + b);
+            if (x0[t] >= T0s && b < H) park(x0[t], b);
+            if (x1[t] >= T0s && b < H && H + b < G2) park(x1[t], H + b);
         }
     }
     __syncthreads();
+    // Pass 2: candidates among the parked survivors become keys
+    const int ns = (int)*nstage;
+    if (ns > 256) {                                         // uniform; the threshold let far too much through
+        __syncthreads();
+        if (tid == 0) *nstage = 0u;
+        return false;
+    }
+    for (int i = tid; i < ns; i += T) {
+        const uint2 hc = stage[i];
+        if (pred((int)hc.y)) {
+            const uint32_t q = atomicAdd(counter, 1u);
+            if (q < 128u) sel.list[q] = ((unsigned long long)((hc.x >> 9) + 1u) << 16) | (unsigned)(G2 - (int)hc.y);
+        }
+    }
+    __syncthreads();
+    if (tid == 0) *nstage = 0u;                             // everyone is past reading it
     const int m = (int)*counter;
     if (m < J || m > 128) return false;                     // uniform over the CTA
     for (int base = 0; base < m; base += T / 4) {           // rank by counting, four threads per key

@@ -26,6 +26,8 @@ CONFIGS = [
     (12, 6, 2, {'packets_factor': 10}, 512, 40),  # CTA mode, free < k on every step: every env goes through the redo list
     (20, 32, 2, {'packets_factor': 1, 'dropzones_factor': 1, 'stations_factor': 1, 'skyscrapers_factor': 1}, 256, 40),   # 32 drones on a small CTA-mode grid
     (64, 32, 5, {'stations_factor': 8, 'skyscrapers_factor': 16}, 24, 12),   # BASELINE large world
+    (16, 4, 7, {}, 256, 24),                     # CTA mode, 15x15 windows: 64-bit packed window codes
+    (24, 3, 11, {}, 128, 16),                    # CTA mode, 23x23 windows (cell-by-cell tiles), odd n: 8-byte aligned tiles
 ]
 
 
