@@ -250,15 +250,18 @@ def run_b200(a):
         peak, peak_src = float(json.load(open(peaks_path))['hbm_gbs']), 'measured (MEASURED_PEAKS.json hbm_gbs)'
     else:
         peak, peak_src = 6650.0, 'fallback (B200_PROFILING.md)'
+    # DRAM traffic of the dominant kernel: ncu --set full captures of exactly this launch shape, summarised in
+    # profiles/step_kernel_traffic.json (one entry per shape)
     traffic = None
     tpath = os.path.join(ROOT, 'profiles', 'step_kernel_traffic.json')
-    is_default = (a.grid, a.drones, a.radius, N_local) == (G, N_DRONES, RADIUS, 1 << 20) and tuple(factors(a).values()) == (3, 2, 2, 3)
-    if os.path.exists(tpath) and is_default:      # ncu --set full capture of exactly this launch shape (profiles/)
+    shape_key = 'G%d_n%d_r%d_f%d-%d-%d-%d_N%d' % ((a.grid, a.drones, a.radius) + tuple(factors(a).values()) + (N_local,))
+    if os.path.exists(tpath):
         try:
-            traffic = json.load(open(tpath)).get('dram_bytes_per_launch')
+            traffic = json.load(open(tpath)).get(shape_key, {}).get('dram_bytes_per_launch')
         except Exception:
             traffic = None
-    kernel_name = ('k_step_warp' if a.grid * a.grid <= 128 else 'k_step_cta') + ' (fused step+get_obs)'
+    kernel_name = ('k_step_warp (fused step+get_obs)' if a.grid * a.grid <= 128 else
+                   'k_step_fast + k_step_cta on its redo list (fused step+get_obs)')
 
     # ---- e2e: the C-ABI call with HOST buffers (actions in, rewards+dones out), per step -------------
     e2e = None

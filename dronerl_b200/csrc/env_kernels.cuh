@@ -921,6 +921,8 @@ __device__ __forceinline__ bool stream_select(Group<T>& grp, const D& d, const S
         const uint32_t i = atomicAdd(nstage, 1u);
         if (i < 256u) stage[i] = make_uint2(o, (uint32_t)cell);
     };
+    // static shapes whose blocks fill the threads exactly need no per-block bounds checks
+    const bool exact = D::kStatic && NB * T == H && 2 * H == G2;
 #pragma unroll 1
     for (int c0 = 0; c0 < NB; c0 += CH) {
         uint32_t x0[CH], x1[CH];
@@ -929,14 +931,14 @@ __device__ __forceinline__ bool stream_select(Group<T>& grp, const D& d, const S
         for (int t = 0; t < CH; ++t) {
             const int hi = H + b0 + t;
             x0[t] = (uint32_t)(b0 + t);
-            x1[t] = hi < G2 ? (uint32_t)hi : 0u;
+            x1[t] = (exact || hi < G2) ? (uint32_t)hi : 0u;
         }
         drl_threefry2x32_n<CH>(k0, k1, x0, x1);
 #pragma unroll
         for (int t = 0; t < CH; ++t) {
             const int b = b0 + t;
-            if (x0[t] >= T0s && b < H) park(x0[t], b);
-            if (x1[t] >= T0s && b < H && H + b < G2) park(x1[t], H + b);
+            if (x0[t] >= T0s && (exact || b < H)) park(x0[t], b);
+            if (x1[t] >= T0s && (exact || (b < H && H + b < G2))) park(x1[t], H + b);
         }
     }
     __syncthreads();
