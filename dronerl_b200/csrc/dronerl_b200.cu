@@ -199,7 +199,7 @@ k_step_fast(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint
     Group<T> grp{reinterpret_cast<unsigned long long*>(smem_raw + c.off_red)};
     const Sel sel = carve_sel(smem_raw, c);
     zero_code(c, sm, threadIdx.x, T);
-    if (threadIdx.x == 0) sel.cnt[1] = sel.cnt[2] = sel.cnt[3] = 0u;
+    if (threadIdx.x == 0) sel.cnt[1] = sel.cnt[2] = sel.cnt[3] = sel.cnt[4] = 0u;
     Stats st;
     unsigned env_steps = 0;
     const D d{c};
@@ -398,7 +398,7 @@ static void carve_layout(DevCfg& c, bool warp_mode, int Q, bool fast, int cta_th
     c.sel_hist = fast ? 0 : 1024;
     c.sel_cap = fast ? 384 : c.sel_maxj + 256;      // J keys plus a generous few histogram bins' worth (fast: 128 keys + 256 parked)
     // CTA mode only: histogram [256] | counters [4] | key list [cap] | rank -> position table [maxj]
-    const int sel_bytes = warp_mode ? 0 : c.sel_hist + 16 + c.sel_cap * 8 + round_up(c.sel_maxj * 2, 16);
+    const int sel_bytes = warp_mode ? 0 : c.sel_hist + 32 + c.sel_cap * 8 + round_up(c.sel_maxj * 2, 16);
     c.off_tile = round_up(c.off_sel + sel_bytes, 128);
     c.group_bytes = c.off_tile + c.tile_bufs * c.tile_stride * (warp_mode ? 1 : cta_threads / 32);
 }

@@ -315,7 +315,7 @@ __device__ __forceinline__ void extract_ranks(Group<T>& grp, int tid, const D& d
 // serial path.
 struct Sel {
     uint32_t* hist;             // [256]
-    uint32_t* cnt;              // [4]
+    uint32_t* cnt;              // [8]: 0 histogram path, 1/2 alternating key counters, 3/4 parked survivors (ground / air)
     unsigned long long* list;   // [cap]
     uint16_t* pos;              // [maxj]  rank -> flat cell
     int cap;
@@ -325,8 +325,8 @@ __device__ __forceinline__ Sel carve_sel(unsigned char* base, const DevCfg& c) {
     Sel s;
     s.hist = reinterpret_cast<uint32_t*>(base + c.off_sel);
     s.cnt = reinterpret_cast<uint32_t*>(base + c.off_sel + c.sel_hist);
-    s.list = reinterpret_cast<unsigned long long*>(base + c.off_sel + c.sel_hist + 16);
-    s.pos = reinterpret_cast<uint16_t*>(base + c.off_sel + c.sel_hist + 16 + (size_t)c.sel_cap * 8);
+    s.list = reinterpret_cast<unsigned long long*>(base + c.off_sel + c.sel_hist + 32);
+    s.pos = reinterpret_cast<uint16_t*>(base + c.off_sel + c.sel_hist + 32 + (size_t)c.sel_cap * 8);
     s.cap = c.sel_cap;
     return s;
 }
@@ -898,53 +898,58 @@ __device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const D
 // the register budget shrinks and more CTAs fit an SM.  Whenever the fast path cannot prove its result
 // (too few or too many survivors, an erasing edge) it reports failure, nothing of the env is written back
 // and the env is stepped again by the general kernel from its untouched state (redo list).
-template <int T, int NB, class D, class P>
-__device__ __forceinline__ bool stream_select(Group<T>& grp, const D& d, const Sel& sel, int tid, uint32_t k0, uint32_t k1,
-                                              int J, int ncand, P&& pred) {
-    constexpr int CH = NB < 4 ? NB : 4;                     // blocks hashed together (interleaved rounds)
-    static_assert(NB % CH == 0, "NB must be 1, 2 or a multiple of 4");
+// Pre-filter threshold on the raw 32-bit words for J winners among about ``ncand`` candidates.
+__device__ __forceinline__ uint32_t select_threshold(int J, int ncand) {
     int sq = 1;
     while (sq * sq < J) ++sq;
     const int target = J + 4 * sq + 8;                      // <= 64 for J <= 32
     uint32_t T0 = 0;
     if (ncand > target) T0 = (uint32_t)(8388608.0f * (1.0f - __fdividef((float)target, (float)ncand)));
-    const uint32_t T0s = T0 << 9;                           // (o >> 9) >= T0  <=>  o >= T0 << 9
-    uint32_t* const counter = sel.cnt + 1 + grp.spar;       // see rank_positions: two alternating counters
-    if (tid == 0) sel.cnt[1 + (grp.spar ^ 1)] = 0u;
-    grp.spar ^= 1;
+    return T0 << 9;                                         // (o >> 9) >= T0  <=>  o >= T0 << 9
+}
+
+// Pass 1 of a streamed selection: threads [first, first + count) of the CTA hash all H blocks of the noise
+// vector of (k0, k1), CH at a time with interleaved rounds (block b of worker j: j + count * i), and park the
+// raw words at or above the threshold, with their cells, in ``stage`` (128 entries; *nstage counts them).
+template <int CH, class D>
+__device__ __forceinline__ void park_pass(const D& d, int worker, int count, uint32_t k0, uint32_t k1, uint32_t T0s, uint2* stage,
+                                          uint32_t* nstage) {
     const int H = d.H(), G2 = d.G2();
-    // Pass 1: hash, compare, and park the rare survivors (raw word + cell) in the upper half of the list; the
-    // candidate test and the key come later, one survivor per thread, so the divergent part of the loop is short.
-    uint2* const stage = reinterpret_cast<uint2*>(sel.list + 128);
-    uint32_t* const nstage = sel.cnt + 3;
     auto park = [&](uint32_t o, int cell) {
         const uint32_t i = atomicAdd(nstage, 1u);
-        if (i < 256u) stage[i] = make_uint2(o, (uint32_t)cell);
+        if (i < 128u) stage[i] = make_uint2(o, (uint32_t)cell);
     };
-    // static shapes whose blocks fill the threads exactly need no per-block bounds checks
-    const bool exact = D::kStatic && NB * T == H && 2 * H == G2;
 #pragma unroll 1
-    for (int c0 = 0; c0 < NB; c0 += CH) {
+    for (int b0 = worker; b0 < H; b0 += count * CH) {
         uint32_t x0[CH], x1[CH];
-        const int b0 = tid * NB + c0;
 #pragma unroll
         for (int t = 0; t < CH; ++t) {
-            const int hi = H + b0 + t;
-            x0[t] = (uint32_t)(b0 + t);
-            x1[t] = (exact || hi < G2) ? (uint32_t)hi : 0u;
+            const int b = b0 + t * count, hi = H + b;
+            x0[t] = (uint32_t)b;
+            x1[t] = hi < G2 ? (uint32_t)hi : 0u;
         }
         drl_threefry2x32_n<CH>(k0, k1, x0, x1);
 #pragma unroll
         for (int t = 0; t < CH; ++t) {
-            const int b = b0 + t;
-            if (x0[t] >= T0s && (exact || b < H)) park(x0[t], b);
-            if (x1[t] >= T0s && (exact || (b < H && H + b < G2))) park(x1[t], H + b);
+            const int b = b0 + t * count;
+            if (x0[t] >= T0s && b < H) park(x0[t], b);
+            if (x1[t] >= T0s && b < H && H + b < G2) park(x1[t], H + b);
         }
     }
-    __syncthreads();
-    // Pass 2: candidates among the parked survivors become keys
+}
+
+// Passes 2 and 3: candidates among the parked survivors become keys, the keys are ranked by counting (four
+// threads per key) and sel.pos[0 .. J) receives the winners.  Call with the whole CTA after a barrier that
+// follows pass 1.  Returns false (uniformly) when the result cannot be proven: fewer than J or more than 128 keys.
+template <int T, class D, class P>
+__device__ __forceinline__ bool select_finish(Group<T>& grp, const D& d, const Sel& sel, int tid, const uint2* stage,
+                                              uint32_t* nstage, int J, P&& pred) {
+    const int G2 = d.G2();
+    uint32_t* const counter = sel.cnt + 1 + grp.spar;       // two alternating key counters: the one in use is zero
+    if (tid == 0) sel.cnt[1 + (grp.spar ^ 1)] = 0u;         // on entry, the other one is re-zeroed for the next call
+    grp.spar ^= 1;
     const int ns = (int)*nstage;
-    if (ns > 256) {                                         // uniform; the threshold let far too much through
+    if (ns > 128) {                                         // uniform; the threshold let far too much through
         __syncthreads();
         if (tid == 0) *nstage = 0u;
         return false;
@@ -975,6 +980,16 @@ __device__ __forceinline__ bool stream_select(Group<T>& grp, const D& d, const S
     return true;
 }
 
+template <int T, int NB, class D, class P>
+__device__ __forceinline__ bool stream_select(Group<T>& grp, const D& d, const Sel& sel, int tid, uint32_t k0, uint32_t k1,
+                                              int J, int ncand, P&& pred) {
+    constexpr int CH = NB < 4 ? NB : 4;
+    uint2* const stage = reinterpret_cast<uint2*>(sel.list + 128);
+    park_pass<CH>(d, tid, T, k0, k1, select_threshold(J, ncand), stage, sel.cnt + 3);
+    __syncthreads();
+    return select_finish<T>(grp, d, sel, tid, stage, sel.cnt + 3, J, pred);
+}
+
 // One env step, fast path.  Same contract as env_step, plus: ``F0`` and the staged ground come from the caller,
 // returns false (uniformly) when the env has to be redone by the general kernel; shared state is then garbage
 // except that sm.code is all zero again.  rewards/dones are written either way (the redo writes the same).
@@ -985,55 +1000,64 @@ __device__ __forceinline__ bool env_step_fast(Group<T>& grp, const DevCfg& c, co
     const int tid = threadIdx.x, lane = threadIdx.x & 31;
     const bool drone_warp = threadIdx.x < 32;
     const int G = d.G(), G2 = d.G2(), n = d.n();
+    uint2* const stage_air = reinterpret_cast<uint2*>(sel.list + 256);
+    uint32_t* const nstage_air = sel.cnt + 4;
+    const int ncand_air = G2 - 1 - c.k_reset[3] - n;        // estimate: cells minus skyscrapers, survivors, the last cell
     DroneOut o;
+    uint32_t sk0 = 0, sk1 = 0, rk0 = 0, rk1 = 0;
     if (drone_warp) {
         o = drone_phase(c, d, sm, lane, rec, act, rewards_e, dones_e, st);
         if (lane == 0) {
             sm.misc[0] = o.mP; sm.misc[1] = o.mD; sm.misc[2] = o.mDone;
             sm.misc[3] = (uint32_t)o.npick | ((uint32_t)o.ndel << 16);
         }
+    } else {
+        // Meanwhile the other warps walk the key chain: key, spawn_key = split(key), twice (env.py:197,224).
+        // (Hashing the spawn_air noise here too, speculatively for the largest J, was measured slower: 3.63 vs 3.45 ms.)
+        split_warp(k0, k1, sk0, sk1);
+        split_warp(k0, k1, rk0, rk1);
+        if (tid == 32) { sm.misc[4] = sk0; sm.misc[5] = sk1; sm.misc[6] = rk0; sm.misc[7] = rk1; }
     }
     __syncthreads();                                        // also: pickup clears are visible
     const uint32_t mP = sm.misc[0], mD = sm.misc[1], mDone = sm.misc[2];
     const int npick = (int)(sm.misc[3] & 0xFFFFu), ndel = (int)(sm.misc[3] >> 16);
+    sk0 = sm.misc[4]; sk1 = sm.misc[5]; rk0 = sm.misc[6]; rk1 = sm.misc[7];
     const int k = c.k_spawn;
     const int F1 = F0 + npick;                              // free cells after the pickups
     const int F2 = F1 - __popc(mP) + ndel;                  // ... after the packet respawn and the delivery clears
-    // the erasing-zeros edges (a fill vector longer than the free cells) belong to the general kernel
-    if (F1 < k || F2 < k) return false;
-    uint32_t sk0 = 0, sk1 = 0;
-    if (mP != 0 || mD != 0 || mDone != 0) split_warp(k0, k1, sk0, sk1);          // key, spawn_key = split(key)
+    bool ok = F1 >= k && F2 >= k;      // the erasing-zeros edges (a fill vector longer than the free cells) are redone
     auto is_free = [&](int cell) { return sm.sg[cell] == 0; };
     // S8 packet respawn (env.py:197-203)
-    if (mP != 0) {
+    if (ok && mP != 0) {
         const int J = 32 - __clz(mP);
-        if (!stream_select<T, NB>(grp, d, sel, tid, sk0, sk1, J, F1, is_free)) return false;
-        for (int j = tid; j < J; j += T) sm.sg[sel.pos[j]] = ((mP >> j) & 1u) ? PACKET : 0;
+        ok = stream_select<T, NB>(grp, d, sel, tid, sk0, sk1, J, F1, is_free);
+        if (ok)
+            for (int j = tid; j < J; j += T) sm.sg[sel.pos[j]] = ((mP >> j) & 1u) ? PACKET : 0;
     }
     // S9 dropzone respawn (env.py:205-212): same spawn_key, the noise is hashed again (deliveries are rare)
-    if (mD != 0) {
+    if (ok && mD != 0) {
         __syncthreads();                                    // mask zeroing comes after the packet spawn's writes
         if (drone_warp && o.del_clear) sm.sg[o.tcell] = 0;
         __syncthreads();
         const int J = 32 - __clz(mD);
-        if (!stream_select<T, NB>(grp, d, sel, tid, sk0, sk1, J, F2, is_free)) return false;
-        for (int j = tid; j < J; j += T) sm.sg[sel.pos[j]] = ((mD >> j) & 1u) ? DROPZONE : 0;
+        ok = stream_select<T, NB>(grp, d, sel, tid, sk0, sk1, J, F2, is_free);
+        if (ok)
+            for (int j = tid; j < J; j += T) sm.sg[sel.pos[j]] = ((mD >> j) & 1u) ? DROPZONE : 0;
     }
     // S11 respawn of done drones (env.py:222-230) and S12 pickup on respawn (env.py:233-241)
     int x = o.x, y = o.y, carry = o.carry;
-    if (mDone != 0) {
-        split_warp(k0, k1, sk0, sk1);                       // key, spawn_key = split(key)  (second split)
+    if (ok && mDone != 0) {
         // p_choice[x, y] = False for survivors (row = x): a bitmap here, one bit per cell
         uint32_t* const sbits = reinterpret_cast<uint32_t*>(sm.code);
         if (drone_warp && o.surv) atomicOr(&sbits[(x * G + y) >> 5], 1u << ((x * G + y) & 31));
+        const int J = 32 - __clz(mDone);
+        park_pass<(NB < 4 ? NB : 4)>(d, tid, T, rk0, rk1, select_threshold(J, ncand_air), stage_air, nstage_air);
         __syncthreads();                                    // also orders the ground writes above
         // no erasing edge on this path, so the skyscrapers are those of the old ground
         auto is_cand = [&](int cell) { return !((sbits[cell >> 5] >> (cell & 31)) & 1u) && sm.sg[cell] != SKY && cell != G2 - 1; };
-        const int J = 32 - __clz(mDone);
-        const bool ok = stream_select<T, NB>(grp, d, sel, tid, sk0, sk1, J, G2 - 1 - c.k_reset[3] - n, is_cand);
+        ok = select_finish<T>(grp, d, sel, tid, stage_air, nstage_air, J, is_cand);
         if (drone_warp && o.surv) sbits[(x * G + y) >> 5] = 0u;   // restore the all-zero invariant
-        if (!ok) return false;
-        if (drone_warp && o.done) {
+        if (ok && drone_warp && o.done) {
             const int pos = sel.pos[lane];
             x = (int)d.divG((uint32_t)pos);                 // rank i -> drone i: x = pos // G, y = pos % G
             y = pos - x * G;
@@ -1046,7 +1070,7 @@ __device__ __forceinline__ bool env_step_fast(Group<T>& grp, const DevCfg& c, co
     }
     if (drone_warp) rec = (uint32_t)x | ((uint32_t)y << 8) | ((uint32_t)carry << 16) | ((uint32_t)o.ch << 24);
     __syncthreads();
-    return true;
+    return ok;
 }
 
 // ---- one env reset (env.py:89-135) -------------------------------------------------------------
