@@ -647,6 +647,7 @@ int drl_create(const drl_config* cfg, drl_env** out) {
     c.ntiles = (n + c.tile_drones - 1) / c.tile_drones;
     c.tile_stride = round_up(c.tile_drones * cell_bytes, 128);
     c.tile_bufs = 1;
+    if (const char* tb = getenv("DRL_TILE_BUFS")) c.tile_bufs = (e->warp_mode && tb[0] == '2') ? 2 : 1;   // A/B switch
     e->envs_per_warp = !e->warp_mode ? 1 : n <= 4 ? DRL_QMAX : n <= 8 ? 4 : n <= 16 ? 2 : 1;
     const int Q = e->envs_per_warp;
     c.sel_maxj = c.k_spawn > n ? c.k_spawn : n;

@@ -27,6 +27,11 @@ CONFIGS = [
     (20, 32, 2, {'packets_factor': 1, 'dropzones_factor': 1, 'stations_factor': 1, 'skyscrapers_factor': 1}, 256, 40),   # 32 drones on a small CTA-mode grid
     (64, 32, 5, {'stations_factor': 8, 'skyscrapers_factor': 16}, 24, 12),   # BASELINE large world
     (16, 4, 7, {}, 256, 24),                     # CTA mode, 15x15 windows: 64-bit packed window codes
+    (5, 1, 1, {}, 1024, 40),                     # a single drone
+    (7, 2, 6, {}, 512, 30),                      # window wider than the grid
+    (11, 16, 1, {'packets_factor': 1, 'dropzones_factor': 1, 'stations_factor': 1, 'skyscrapers_factor': 1}, 512, 30),   # warp mode, 2 envs per warp
+    (11, 20, 1, {'packets_factor': 1, 'dropzones_factor': 1, 'stations_factor': 1, 'skyscrapers_factor': 1}, 512, 30),   # warp mode, 1 env per warp
+    (90, 8, 2, {}, 24, 10),                      # largest grid: 16 threefry blocks per thread
     (24, 3, 11, {}, 128, 16),                    # CTA mode, 23x23 windows (cell-by-cell tiles), odd n: 8-byte aligned tiles
 ]
 

@@ -1,0 +1,119 @@
+// Micro-benchmark: how fast can one B200 write an obs-shaped stream of S-byte records from shared memory?
+//   mode 0  one cp.async.bulk.global.shared::cta per record (what the step kernel does), record stride = S
+//   mode 1  coalesced st.global.v4 by the warp, record stride = S
+//   mode 2  bulk store, record stride padded to a multiple of 128 B (line-aligned destinations)
+//   mode 3  bulk store split in two halves (two ops per record)
+// Each warp owns records w, w + nwarps, ...; it waits for its previous store to release the buffer
+// (wait_group.read 0), touches the buffer (a few stores, like a tile compose) and stores again.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o bulk_store_bench bulk_store_bench.cu
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+
+__global__ void __launch_bounds__(256, 3) k_store(float* __restrict__ out, long long nrec, int S, long long stride, int mode, int touch, uint4* __restrict__ ground, uint32_t* __restrict__ drones, float* __restrict__ rewards, unsigned char* __restrict__ dones, const uint2* __restrict__ keys, const int* __restrict__ actions, int small, int hint) {
+    unsigned long long pol_last, pol_first;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_last));
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_first));
+    extern __shared__ __align__(128) unsigned char smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int bufsz = (S + 127) / 128 * 128;
+    float4* buf = reinterpret_cast<float4*>(smem + (size_t)warp * bufsz);
+    for (int i = lane; i < bufsz / 16; i += 32) buf[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    __syncwarp();
+    const long long nw = (long long)gridDim.x * 8, w0 = (long long)blockIdx.x * 8 + warp;
+    const uint32_t saddr = (uint32_t)__cvta_generic_to_shared(buf);
+    uint4 ngv = make_uint4(0, 0, 0, 0); uint32_t ndr = 0; int nac = 0; uint2 nkk = make_uint2(0, 0);
+    if ((small & 4) && w0 < nrec) { if (lane < 6) ngv = ground[w0 * 6 + lane]; if (lane < 4) ndr = drones[w0 * 4 + lane]; if (lane == 0) { nac = actions[w0]; nkk = keys[w0]; } }
+    for (long long r = w0; r < nrec; r += nw) {
+        char* dst = reinterpret_cast<char*>(out) + r * stride;
+        if (mode != 1) {
+            if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            __syncwarp();
+        }
+        uint4 gv = make_uint4(0, 0, 0, 0); uint32_t dr = 0; int ac = 0; uint2 kk = make_uint2(0, 0);
+        if (small & 4) {
+            gv = ngv; dr = ndr; ac = nac; kk = nkk;
+            const long long rn = r + nw;
+            if (rn < nrec) {
+                if (hint) {
+                    if (lane < 6) asm volatile("ld.global.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;" : "=r"(ngv.x), "=r"(ngv.y), "=r"(ngv.z), "=r"(ngv.w) : "l"(ground + rn * 6 + lane), "l"(pol_last));
+                    if (lane < 4) asm volatile("ld.global.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(ndr) : "l"(drones + rn * 4 + lane), "l"(pol_last));
+                } else {
+                if (lane < 6) ngv = ground[rn * 6 + lane];
+                if (lane < 4) ndr = drones[rn * 4 + lane];
+                }
+                if (lane == 0) { nac = actions[rn]; nkk = keys[rn]; }
+            }
+        } else if (small & 1) {
+            if (lane < 6) gv = ground[r * 6 + lane];
+            if (lane < 4) dr = drones[r * 4 + lane];
+            if (lane == 0) { ac = actions[r]; kk = keys[r]; }
+        }
+        for (int t = 0; t < touch; ++t) buf[(lane + 32 * t) % (bufsz / 16)] = make_float4((float)r + (float)(gv.x + dr + ac + kk.x), 0.f, 0.f, 0.f);
+        if (small & 2) {
+            if (hint) {
+                if (lane < 6) { gv.x ^= 1u; asm volatile("st.global.L2::cache_hint.v4.u32 [%0], {%1,%2,%3,%4}, %5;" :: "l"(ground + r * 6 + lane), "r"(gv.x), "r"(gv.y), "r"(gv.z), "r"(gv.w), "l"(pol_last) : "memory"); }
+                if (lane < 4) { asm volatile("st.global.L2::cache_hint.u32 [%0], %1, %2;" :: "l"(drones + r * 4 + lane), "r"(dr + 1u), "l"(pol_last) : "memory"); rewards[r * 4 + lane] = 1.0f; }
+            } else {
+            if (lane < 6) { gv.x ^= 1u; ground[r * 6 + lane] = gv; }
+            if (lane < 4) { drones[r * 4 + lane] = dr + 1u; rewards[r * 4 + lane] = 1.0f; }
+            }
+            if (lane == 0) reinterpret_cast<uint32_t*>(dones)[r] = 0x01010101u;
+        }
+        if (mode == 1) {
+            __syncwarp();
+            float4* g = reinterpret_cast<float4*>(dst);
+            for (int i = lane; i < S / 16; i += 32) g[i] = buf[i];
+            __syncwarp();
+        } else {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) {
+                if (mode == 3) {
+                    const int h = (S / 2) & ~15;
+                    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(saddr), "r"(h) : "memory");
+                    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst + h), "r"(saddr + h), "r"(S - h) : "memory");
+                } else {
+                    if (hint) asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(dst), "r"(saddr), "r"(S), "l"(pol_first) : "memory");
+                    else asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(saddr), "r"(S) : "memory");
+                }
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+        }
+    }
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
+int main() {
+    const long long nrec = 1 << 20;
+    float* out;
+    cudaMalloc(&out, (size_t)nrec * 9472 + 4096);
+    uint4* ground; uint32_t* drones; float* rewards; unsigned char* dones; uint2* keys; int* actions;
+    cudaMalloc(&ground, nrec * 96); cudaMalloc(&drones, nrec * 16); cudaMalloc(&rewards, nrec * 16); cudaMalloc(&dones, nrec * 4); cudaMalloc(&keys, nrec * 8); cudaMalloc(&actions, nrec * 4);
+    cudaMemset(ground, 0, nrec * 96); cudaMemset(drones, 0, nrec * 16); cudaMemset(keys, 0, nrec * 8); cudaMemset(actions, 0, nrec * 4);
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    const int sizes[] = {4704};
+    for (int hint : {0, 1}) for (int small : {0, 6}) for (int touch : {8}) {
+        for (int S : sizes) {
+            for (int mode = 0; mode < 1; ++mode) {
+                const long long stride = mode == 2 ? (S + 127) / 128 * 128 : S;
+                const int smem = 8 * ((S + 127) / 128 * 128);
+                cudaFuncSetAttribute(k_store, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+                for (int rep = 0; rep < 3; ++rep) k_store<<<444, 256, smem>>>(out, nrec, S, stride, mode, touch, ground, drones, rewards, dones, keys, actions, small, hint);
+                cudaEventRecord(e0);
+                for (int rep = 0; rep < 5; ++rep) k_store<<<444, 256, smem>>>(out, nrec, S, stride, mode, touch, ground, drones, rewards, dones, keys, actions, small, hint);
+                cudaEventRecord(e1);
+                cudaEventSynchronize(e1);
+                float ms;
+                cudaEventElapsedTime(&ms, e0, e1);
+                ms /= 5;
+                printf("hint %d small %d touch %d S %5d mode %d stride %5lld: %.3f ms  %.0f GB/s  (%s)\n", hint, small, touch, S, mode, stride, ms, (double)nrec * S / ms / 1e6,
+                       cudaGetErrorString(cudaGetLastError()));
+            }
+        }
+    }
+    return 0;
+}

@@ -11,7 +11,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 
-__global__ void __launch_bounds__(256, 3) k_store(float* __restrict__ out, long long nrec, int S, long long stride, int mode, int touch) {
+__global__ void __launch_bounds__(256, 3) k_store(float* __restrict__ out, long long nrec, int S, long long stride, int mode, int touch, uint4* __restrict__ ground, uint32_t* __restrict__ drones, float* __restrict__ rewards, unsigned char* __restrict__ dones, const uint2* __restrict__ keys, const int* __restrict__ actions, int small, int GV) {
     extern __shared__ __align__(128) unsigned char smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int bufsz = (S + 127) / 128 * 128;
@@ -20,13 +20,34 @@ __global__ void __launch_bounds__(256, 3) k_store(float* __restrict__ out, long 
     __syncwarp();
     const long long nw = (long long)gridDim.x * 8, w0 = (long long)blockIdx.x * 8 + warp;
     const uint32_t saddr = (uint32_t)__cvta_generic_to_shared(buf);
+    uint4 ngv = make_uint4(0, 0, 0, 0); uint32_t ndr = 0; int nac = 0; uint2 nkk = make_uint2(0, 0);
+    if ((small & 4) && w0 < nrec) { if (lane < GV) ngv = ground[w0 * GV + lane]; if (lane < 4) ndr = drones[w0 * 4 + lane]; if (lane == 0) { nac = actions[w0]; nkk = keys[w0]; } }
     for (long long r = w0; r < nrec; r += nw) {
         char* dst = reinterpret_cast<char*>(out) + r * stride;
         if (mode != 1) {
             if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
             __syncwarp();
         }
-        for (int t = 0; t < touch; ++t) buf[(lane + 32 * t) % (bufsz / 16)] = make_float4((float)r, 0.f, 0.f, 0.f);
+        uint4 gv = make_uint4(0, 0, 0, 0); uint32_t dr = 0; int ac = 0; uint2 kk = make_uint2(0, 0);
+        if (small & 4) {
+            gv = ngv; dr = ndr; ac = nac; kk = nkk;
+            const long long rn = r + nw;
+            if (rn < nrec) {
+                if (lane < GV) ngv = ground[rn * GV + lane];
+                if (lane < 4) ndr = drones[rn * 4 + lane];
+                if (lane == 0) { nac = actions[rn]; nkk = keys[rn]; }
+            }
+        } else if (small & 1) {
+            if (lane < GV) gv = ground[r * GV + lane];
+            if (lane < 4) dr = drones[r * 4 + lane];
+            if (lane == 0) { ac = actions[r]; kk = keys[r]; }
+        }
+        for (int t = 0; t < touch; ++t) buf[(lane + 32 * t) % (bufsz / 16)] = make_float4((float)r + (float)(gv.x + dr + ac + kk.x), 0.f, 0.f, 0.f);
+        if (small & 2) {
+            if (lane < GV) { gv.x ^= 1u; ground[r * GV + lane] = gv; }
+            if (lane < 4) { drones[r * 4 + lane] = dr + 1u; rewards[r * 4 + lane] = 1.0f; }
+            if (lane == 0) reinterpret_cast<uint32_t*>(dones)[r] = 0x01010101u;
+        }
         if (mode == 1) {
             __syncwarp();
             float4* g = reinterpret_cast<float4*>(dst);
@@ -54,25 +75,28 @@ int main() {
     const long long nrec = 1 << 20;
     float* out;
     cudaMalloc(&out, (size_t)nrec * 9472 + 4096);
+    uint4* ground; uint32_t* drones; float* rewards; unsigned char* dones; uint2* keys; int* actions;
+    cudaMalloc(&ground, nrec * 96); cudaMalloc(&drones, nrec * 16); cudaMalloc(&rewards, nrec * 16); cudaMalloc(&dones, nrec * 4); cudaMalloc(&keys, nrec * 8); cudaMalloc(&actions, nrec * 4);
+    cudaMemset(ground, 0, nrec * 96); cudaMemset(drones, 0, nrec * 16); cudaMemset(keys, 0, nrec * 8); cudaMemset(actions, 0, nrec * 4);
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0);
     cudaEventCreate(&e1);
     const int sizes[] = {4704};
-    for (int touch : {0, 4, 10, 20, 40}) {
+    for (int GV : {6, 3, 2}) for (int small : {6}) for (int touch : {8}) {
         for (int S : sizes) {
-            for (int mode = 0; mode < 2; ++mode) {
+            for (int mode = 0; mode < 1; ++mode) {
                 const long long stride = mode == 2 ? (S + 127) / 128 * 128 : S;
                 const int smem = 8 * ((S + 127) / 128 * 128);
                 cudaFuncSetAttribute(k_store, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-                for (int rep = 0; rep < 3; ++rep) k_store<<<444, 256, smem>>>(out, nrec, S, stride, mode, touch);
+                for (int rep = 0; rep < 3; ++rep) k_store<<<444, 256, smem>>>(out, nrec, S, stride, mode, touch, ground, drones, rewards, dones, keys, actions, small, GV);
                 cudaEventRecord(e0);
-                for (int rep = 0; rep < 5; ++rep) k_store<<<444, 256, smem>>>(out, nrec, S, stride, mode, touch);
+                for (int rep = 0; rep < 5; ++rep) k_store<<<444, 256, smem>>>(out, nrec, S, stride, mode, touch, ground, drones, rewards, dones, keys, actions, small, GV);
                 cudaEventRecord(e1);
                 cudaEventSynchronize(e1);
                 float ms;
                 cudaEventElapsedTime(&ms, e0, e1);
                 ms /= 5;
-                printf("touch %d S %5d mode %d stride %5lld: %.3f ms  %.0f GB/s  (%s)\n", touch, S, mode, stride, ms, (double)nrec * S / ms / 1e6,
+                printf("GV %d small %d touch %d S %5d mode %d stride %5lld: %.3f ms  %.0f GB/s  (%s)\n", GV, small, touch, S, mode, stride, ms, (double)nrec * S / ms / 1e6,
                        cudaGetErrorString(cudaGetLastError()));
             }
         }
