@@ -44,6 +44,7 @@ SYMBOLS = {
     'drl_set_obs_drones': (ctypes.c_int, [_vp, _i32]),
     'drl_reset': (ctypes.c_int, [_vp, _vp, _vp]),
     'drl_step': (ctypes.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    'drl_step_keyed': (ctypes.c_int, [_vp, c_u32p, c_u32p, _i32, _vp, _vp, _vp, _vp, _vp]),
     'drl_get_obs': (ctypes.c_int, [_vp, _vp, _vp]),
     'drl_step_host': (ctypes.c_int, [_vp, c_u32p, _vp, _vp, _vp, _vp, _vp, _vp]),
     'drl_rollout_random': (ctypes.c_int, [_vp, c_u32p, _i32, _i32, _i64, _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -147,10 +147,11 @@ k_step_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint3
         int act = 4;
         if ((int)threadIdx.x < n) {
             rec = drones[e * n + threadIdx.x];
-            act = actions[e * n + threadIdx.x];
+            act = c.act_mode ? derive_action(c, e, (int)threadIdx.x) : (int)actions[e * n + threadIdx.x];
         }
-        const uint2 kk = *reinterpret_cast<const uint2*>(keys + 2 * e);
+        if (c.key_mode && warp == 1 && lane < 2) sm.misc[8 + lane] = derive_key_word(c, e, lane);   // published by the barrier below
         const int F0 = grp.sum(zc) - (GS - d.G2());
+        const uint2 kk = c.key_mode ? make_uint2(sm.misc[8], sm.misc[9]) : *reinterpret_cast<const uint2*>(keys + 2 * e);
         env_step<T, NB>(grp, c, d, sm, sel, validm, F0, rec, act, kk.x, kk.y, rewards + e * n, dones + e * n, st);
         for (int i = threadIdx.x; i < nvec; i += T)
             reinterpret_cast<uint4*>(ground + e * GS)[i] = reinterpret_cast<const uint4*>(sm.sg)[i];
@@ -223,10 +224,11 @@ k_step_fast(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint
         int act = 4;
         if ((int)threadIdx.x < n) {
             rec = drones[e * n + threadIdx.x];
-            act = actions[e * n + threadIdx.x];
+            act = c.act_mode ? derive_action(c, e, (int)threadIdx.x) : (int)actions[e * n + threadIdx.x];
         }
-        const uint2 kk = *reinterpret_cast<const uint2*>(keys + 2 * e);
+        if (c.key_mode && warp == 1 && lane < 2) sm.misc[8 + lane] = derive_key_word(c, e, lane);   // published by the barrier below
         const int F0 = grp.sum(zc) - (GS - d.G2());
+        const uint2 kk = c.key_mode ? make_uint2(sm.misc[8], sm.misc[9]) : *reinterpret_cast<const uint2*>(keys + 2 * e);
         const Stats before = st;
         const bool ok = env_step_fast<T, NB>(grp, c, d, sm, sel, F0, rec, act, kk.x, kk.y, rewards + e * n, dones + e * n, st);
         if (ok) {
@@ -393,7 +395,7 @@ static void carve_layout(DevCfg& c, bool warp_mode, int Q, bool fast, int cta_th
     c.off_sdr = c.off_code + (fast ? round_up((c.G2 + 31) / 32 * 4, 16) : Q * round_up(c.G2, 16));
     c.off_sdf = c.off_sdr + 128;
     c.off_misc = c.off_sdf + 128;
-    c.off_red = c.off_misc + 32;
+    c.off_red = c.off_misc + 48;
     c.off_sel = round_up(c.off_red + (warp_mode ? 0 : 2 * (cta_threads / 32) * 8), 16);
     c.sel_hist = fast ? 0 : 1024;
     c.sel_cap = fast ? 384 : c.sel_maxj + 256;      // J keys plus a generous few histogram bins' worth (fast: 128 keys + 256 parked)
@@ -527,15 +529,40 @@ static int configure_launches(drl_env* e) {
 // kernel followed by the general kernel on the fast kernel's redo list (``slot`` < 16 names the list header, so
 // launches that overlap on different streams use different ones).  Returns DRL_OK and adds the kernels launched
 // to *launches.
+struct StepKeys {              // drl_step_keyed: host-side keys hashed inside the kernel instead of key/action arrays
+    const uint32_t* parent;    // per-env keys = split(parent, N_global)[global index]; nullptr: d_keys holds them
+    const uint32_t* action;    // actions = randint(action, (N_global, n), 0, span); nullptr: d_actions holds them
+    int span;
+};
+
+static void fill_derivation(const drl_env* env, DevCfg& dc, long long first, const StepKeys* sk) {
+    dc.key_mode = dc.act_mode = 0;
+    dc.Ng = env->cfg.num_envs_global;
+    dc.goff = env->cfg.env_offset + first;
+    if (!sk) return;
+    if (sk->parent) { dc.key_mode = 1; dc.pk0 = sk->parent[0]; dc.pk1 = sk->parent[1]; }
+    if (sk->action) {
+        uint32_t k1[2], k2[2];
+        drl_split2(sk->action, k1, k2);                    // _randint: k1, k2 = split(key)
+        dc.act_mode = 1;
+        dc.ak[0] = k1[0]; dc.ak[1] = k1[1]; dc.ak[2] = k2[0]; dc.ak[3] = k2[1];
+        dc.act_span = (uint32_t)sk->span;
+        uint32_t mult = 65536u % dc.act_span;
+        dc.act_mult = (mult * mult) % dc.act_span;
+    }
+}
+
 static int launch_step(drl_env* env, long long first, long long count, const uint32_t* d_keys, const int8_t* d_actions,
-                       float* d_rewards, uint8_t* d_dones, float* d_obs, cudaStream_t s, int slot, int* launches) {
+                       float* d_rewards, uint8_t* d_dones, float* d_obs, cudaStream_t s, int slot, int* launches,
+                       const StepKeys* sk = nullptr) {
     DevCfg dc = env->dc;
     dc.N = count;
+    fill_derivation(env, dc, first, sk);
     const long long n = dc.n;
     uint8_t* ground = env->d_ground + first * dc.GS;
     uint32_t* drones = env->d_drones + first * n;
-    const uint32_t* keys = d_keys + 2 * first;
-    const int8_t* actions = d_actions + first * n;
+    const uint32_t* keys = dc.key_mode ? nullptr : d_keys + 2 * first;
+    const int8_t* actions = dc.act_mode ? nullptr : d_actions + first * n;
     float* rewards = d_rewards + first * n;
     uint8_t* dones = d_dones + first * n;
     float* obs = d_obs ? d_obs + first * dc.obs_n * dc.W2 * 6 : nullptr;
@@ -558,6 +585,7 @@ static int launch_step(drl_env* env, long long first, long long count, const uin
         fdc.N = count;
         fdc.obs_n = dc.obs_n;
         fdc.ntiles = dc.ntiles;
+        fill_derivation(env, fdc, first, sk);
         int rc = launch(env, "fast step kernel", ff, (int)(count < rf ? count : rf), kFastThreads, fdc.group_bytes, (void*)s, fdc,
                         ground, drones, keys, actions, rewards, dones, obs, env->d_stats, hdr, list);
         if (rc) return rc;
@@ -830,6 +858,21 @@ int drl_step(drl_env* env, const void* d_keys, const void* d_actions, void* d_re
                        (float*)d_obs, (cudaStream_t)stream, 0, nullptr);
 }
 
+int drl_step_keyed(drl_env* env, const uint32_t key[2], const uint32_t action_key[2], int32_t maxval, const void* d_actions,
+                   void* d_rewards, void* d_dones, void* d_obs, void* stream) {
+    if (!env || !key || !d_rewards || !d_dones || (!action_key && !d_actions)) return DRL_EINVAL;
+    if (!env->d_ground) return fail(env, DRL_ESTATE, "drl_step_keyed: state not bound (call drl_bind_state)%s");
+    if ((uintptr_t)d_obs & 7) return fail(env, DRL_EINVAL, "drl_step_keyed: obs must be 8-byte aligned%s");
+    if (action_key && (maxval < 1 || maxval > 127)) return fail(env, DRL_EINVAL, "drl_step_keyed: maxval must be in 1..127%s");
+    if (action_key && env->cfg.num_envs_global * env->dc.n >= (1ll << 32))
+        return fail(env, DRL_EINVAL, "drl_step_keyed: too many actions (>= 2^32)%s");
+    if (env->cfg.num_envs_global > (1ll << 30)) return fail(env, DRL_EINVAL, "drl_step_keyed: too many envs (> 2^30)%s");
+    CUDA_TRY(env, cudaSetDevice(env->cfg.device));
+    const StepKeys sk = {key, action_key, (int)maxval};
+    return launch_step(env, 0, env->dc.N, nullptr, (const int8_t*)d_actions, (float*)d_rewards, (uint8_t*)d_dones, (float*)d_obs,
+                       (cudaStream_t)stream, 0, nullptr, &sk);
+}
+
 int drl_get_obs(drl_env* env, void* d_obs, void* stream) {
     if (!env || !d_obs) return DRL_EINVAL;
     if (!env->d_ground) return fail(env, DRL_ESTATE, "drl_get_obs: state not bound (call drl_bind_state)%s");
@@ -867,8 +910,7 @@ int drl_step_host(drl_env* env, const uint32_t key[2], const int8_t* h_actions, 
     const DevCfg& c = env->dc;
     const long long n = c.n;
     cudaStream_t s = (cudaStream_t)stream;
-    rc = drl_split_keys(env, key, env->s_keys, stream);
-    if (rc) return rc;
+    const StepKeys sk = {key, nullptr, 0};                          // per-env keys are hashed inside the step kernel
     CUDA_TRY(env, cudaEventRecord(env->pipe_begin, s));
     // chunks of a whole number of 1024-env blocks: H2D actions -> step+obs -> D2H rewards, dones (, obs)
     const long long kMinChunk = 32768;
@@ -882,8 +924,8 @@ int drl_step_host(drl_env* env, const uint32_t key[2], const int8_t* h_actions, 
         cudaStream_t ps = env->pipe_stream[used & 1];
         if (used < 2) CUDA_TRY(env, cudaStreamWaitEvent(ps, env->pipe_begin, 0));
         CUDA_TRY(env, cudaMemcpyAsync(env->s_actions + first * n, h_actions + first * n, count * n, cudaMemcpyHostToDevice, ps));
-        rc = launch_step(env, first, count, env->s_keys, env->s_actions, env->s_rewards, env->s_dones, (float*)d_obs, ps, 1 + used,
-                         nullptr);
+        rc = launch_step(env, first, count, nullptr, env->s_actions, env->s_rewards, env->s_dones, (float*)d_obs, ps, 1 + used,
+                         nullptr, &sk);
         if (rc) return rc;
         CUDA_TRY(env, cudaMemcpyAsync(h_rewards + first * n, env->s_rewards + first * n, count * n * 4, cudaMemcpyDeviceToHost, ps));
         CUDA_TRY(env, cudaMemcpyAsync(h_dones + first * n, env->s_dones + first * n, count * n, cudaMemcpyDeviceToHost, ps));
@@ -903,19 +945,41 @@ int drl_rollout_random(drl_env* env, uint32_t rng[2], int32_t steps, int32_t res
                        void* d_actions, void* d_rewards, void* d_dones, void* d_obs, void* stream) {
     if (!env || !rng || steps < 0 || !d_keys || !d_actions) return DRL_EINVAL;
     int launches = 0;
+    const char* nf = getenv("DRL_NO_FUSE");                 // A/B switch: separate randint / key-split kernels
+    const bool fused = !(nf && nf[0] == '1') && d_rewards && d_dones && env->d_ground &&
+                       env->cfg.num_envs_global * env->dc.n < (1ll << 32);
+    const char* fa = getenv("DRL_FUSE_ACTIONS");
+    const bool fuse_actions = fused && fa && fa[0] == '1';
     for (int32_t t = 0; t < steps; ++t) {
         uint32_t nk[2], sub[2];
         drl_split2(rng, nk, sub);                                  // rng, key = split(rng)   train_jax.py:43
         rng[0] = nk[0]; rng[1] = nk[1];
-        int rc = drl_randint_actions(env, sub, 5, d_actions, stream);   // randint(key, (N, n), 0, 5)  :44
-        if (rc) return rc;
-        drl_split2(rng, nk, sub);                                  // rng, key = split(rng)   :52
+        uint32_t akey[2] = {sub[0], sub[1]};                       // randint(key, (N, n), 0, 5)     :44
+        drl_split2(rng, nk, sub);                                  // rng, key = split(rng)          :52
         rng[0] = nk[0]; rng[1] = nk[1];
-        rc = drl_split_keys(env, sub, d_keys, stream);             // split(key, N)           :53
-        if (rc) return rc;
-        rc = drl_step(env, d_keys, d_actions, d_rewards, d_dones, d_obs, stream);   // :54-55
-        if (rc) return rc;
-        launches += 2 + (pick_fast(env) ? 2 : 1);     // randint, key split, step (fast + general kernel in CTA mode)
+        int rc;
+        if (fused) {
+            // split(key, N) (:53) is hashed inside the step + get_obs kernel (:54-55): the per-env keys never exist in
+            // memory.  (Hashing the actions there too is supported -- drl_step_keyed -- but measured slower than the
+            // separate randint kernel: 1.12 vs 1.06 ms per step at 1M envs; DRL_FUSE_ACTIONS=1 turns it on.)
+            if (!fuse_actions) {
+                rc = drl_randint_actions(env, akey, 5, d_actions, stream);
+                if (rc) return rc;
+                launches += 1;
+            }
+            const StepKeys sk = {sub, fuse_actions ? akey : nullptr, 5};
+            rc = launch_step(env, 0, env->dc.N, nullptr, (const int8_t*)d_actions, (float*)d_rewards, (uint8_t*)d_dones,
+                             (float*)d_obs, (cudaStream_t)stream, 0, &launches, &sk);
+            if (rc) return rc;
+        } else {
+            rc = drl_randint_actions(env, akey, 5, d_actions, stream);
+            if (rc) return rc;
+            rc = drl_split_keys(env, sub, d_keys, stream);             // split(key, N)           :53
+            if (rc) return rc;
+            rc = drl_step(env, d_keys, d_actions, d_rewards, d_dones, d_obs, stream);   // :54-55
+            if (rc) return rc;
+            launches += 2 + (pick_fast(env) ? 2 : 1);     // randint, key split, step (fast + general kernel in CTA mode)
+        }
         drl_split2(rng, nk, sub);                                  // rng, key = split(rng)   :82 (the trainer's batch key)
         rng[0] = nk[0]; rng[1] = nk[1];
         if (reset_every > 0 && (step0 + t) % reset_every == 0) {   // :101-113 (resets with the carried rng itself)

@@ -60,7 +60,26 @@ struct DevCfg {
     int sel_hist, sel_cap, sel_maxj;   // CTA mode: bytes of histogram, capacity of the key list, of the rank -> position table
     int group_bytes;           // warp mode: bytes per warp; CTA mode: bytes per CTA
     long long N;               // local envs
+    // in-kernel key / action derivation (drl_step_keyed): the trainer's jax.random streams by GLOBAL env index
+    int key_mode;              // 0: per-env keys from memory; 1: keys[e] = split(pk, Ng)[goff + e] hashed in the kernel
+    int act_mode;              // 0: actions from memory; 1: randint(key, (Ng, n), 0, act_span) hashed in the kernel
+    uint32_t pk0, pk1;         // parent key of the per-env keys (train_jax.py:52-53)
+    uint32_t ak[4];            // k1, k2 = split(action key) of _randint (train_jax.py:43-44)
+    uint32_t act_span, act_mult;
+    long long Ng, goff;        // global env count, global index of this launch's env 0
 };
+
+// keys[e] word w of jax.random.split(parent, Ng)[goff + e]  (train_jax.py:53)
+__device__ __forceinline__ uint32_t derive_key_word(const DevCfg& c, long long e, int w) {
+    return drl_random_bits_at(c.pk0, c.pk1, (uint64_t)(2 * c.Ng), (uint64_t)(2 * (c.goff + e) + w));
+}
+// int(jax.random.randint(key, (Ng, n), 0, span))[goff + e, j]: _randint's two-draw reduction (train_jax.py:44)
+__device__ __forceinline__ int derive_action(const DevCfg& c, long long e, int j) {
+    const uint64_t total = (uint64_t)(c.Ng * c.n), a = (uint64_t)((c.goff + e) * c.n + j);
+    const uint32_t hi = drl_random_bits_at(c.ak[0], c.ak[1], total, a);
+    const uint32_t lo = drl_random_bits_at(c.ak[2], c.ak[3], total, a);
+    return (int)(((hi % c.act_span) * c.act_mult + (lo % c.act_span)) % c.act_span);
+}
 
 struct Stats {
     unsigned dones = 0, crashes = 0, pickups = 0, deliveries = 0, charging = 0, respawn_pickups = 0;

@@ -70,11 +70,18 @@ __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsi
             if (sub < nq) {
                 if (li < n) {
                     nxt.rec = drones[(e0 + sub) * n + li];
-                    nxt.act = actions[(e0 + sub) * n + li];
+                    nxt.act = c.act_mode ? derive_action(c, e0 + sub, li) : (int)actions[(e0 + sub) * n + li];
                 }
-                const uint2 kk = *reinterpret_cast<const uint2*>(keys + 2 * (e0 + sub));
-                nxt.k0 = kk.x;
-                nxt.k1 = kk.y;
+                if (!c.key_mode) {
+                    const uint2 kk = *reinterpret_cast<const uint2*>(keys + 2 * (e0 + sub));
+                    nxt.k0 = kk.x;
+                    nxt.k1 = kk.y;
+                }
+            }
+            if (c.key_mode) {       // lanes 0 and 1 of each env hash one key word each (S >= 2)
+                const uint32_t w = derive_key_word(c, min(e0 + sub, c.N - 1), li & 1);
+                nxt.k0 = __shfl_sync(FULL, w, sub * S);
+                nxt.k1 = __shfl_sync(FULL, w, sub * S + (S > 1 ? 1 : 0));
             }
         }
     };

@@ -26,7 +26,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from .params import DroneEnvParams
+from .params import Action, DroneEnvParams
 from .state import DroneEnvState
 
 
@@ -162,28 +162,43 @@ class DeliveryDrones:
             h.check(h.lib.drl_reset(h.ptr, _vp(keys), _stream()))
         return state
 
-    def step(self, key, state: DroneEnvState, actions, params: DroneEnvParams, return_obs=False, obs_drones=None):
+    def step(self, key, state: DroneEnvState, actions, params: DroneEnvParams, return_obs=False, obs_drones=None,
+             action_key=None):
         """``env.step(key, state, actions, params)`` / its vmap -- env.py:137-250.
 
         Returns ``(state, rewards float32, dones bool)``; with ``return_obs=True`` the observation of
         the new state (``get_obs``, env.py:274-309) is produced by the same kernel and appended;
         ``obs_drones=k`` renders only the first k drones' windows (``obs[:, :k]``, train_jax.py:56).
+        A single parent ``key`` on a batched state is ``vmap(step)(split(key, N), ...)`` (train_jax.py:52-54)
+        with the per-env keys hashed inside the kernel; ``actions=None, action_key=k`` additionally takes the
+        actions from ``jax.random.randint(k, (N, n), 0, 5)`` (train_jax.py:43-44), also hashed in the kernel.
         """
         device = state.device
         N, n = state.num_envs, params.n_drones
         with torch.cuda.device(device):
             h = self._state_handle(state, params, obs_drones if return_obs else None)
-            if not state.batched:
-                keys = torch.from_numpy(_host_key(key).reshape(1, 2).copy()).to(device)
+            keyed = state.batched and _is_single_key(key)
+            if actions is None:
+                if not keyed or action_key is None:
+                    raise ValueError('actions=None needs a batched state, a single parent key and an action_key')
+                acts = None
             else:
-                keys = self._env_keys(h, key, N, device)
-            if not isinstance(actions, torch.Tensor):
-                actions = torch.as_tensor(np.asarray(actions))
-            acts = actions.to(device=device, dtype=torch.int8).reshape(N, n).contiguous()
+                if not isinstance(actions, torch.Tensor):
+                    actions = torch.as_tensor(np.asarray(actions))
+                acts = actions.to(device=device, dtype=torch.int8).reshape(N, n).contiguous()
             rewards = torch.empty((N, n), dtype=torch.float32, device=device)
             dones = torch.empty((N, n), dtype=torch.uint8, device=device)
             obs = self._obs_buffer(state, params, obs_drones) if return_obs else None
-            h.check(h.lib.drl_step(h.ptr, _vp(keys), _vp(acts), _vp(rewards), _vp(dones), _vp(obs), _stream()))
+            if keyed:
+                ak = _lib.key_array(_host_key(action_key)) if acts is None else None
+                h.check(h.lib.drl_step_keyed(h.ptr, _lib.key_array(_host_key(key)), ak, Action.num_actions(), _vp(acts),
+                                             _vp(rewards), _vp(dones), _vp(obs), _stream()))
+            else:
+                if not state.batched:
+                    keys = torch.from_numpy(_host_key(key).reshape(1, 2).copy()).to(device)
+                else:
+                    keys = self._env_keys(h, key, N, device)
+                h.check(h.lib.drl_step(h.ptr, _vp(keys), _vp(acts), _vp(rewards), _vp(dones), _vp(obs), _stream()))
         dones = dones.view(torch.bool)
         if not state.batched:
             rewards, dones = rewards[0], dones[0]

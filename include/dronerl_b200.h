@@ -147,6 +147,14 @@ int drl_reset(drl_env* env, const void* d_keys, void* stream);
 int drl_step(drl_env* env, const void* d_keys, const void* d_actions, void* d_rewards, void* d_dones,
              void* d_obs, void* stream);
 
+/* drl_step with the per-env keys -- and optionally the actions -- hashed INSIDE the step kernel, so neither array
+ * exists in memory (0 bytes of key / action traffic, no derivation kernels):
+ *   keys[e]    = jax.random.split(key, num_envs_global)[env_offset + e]                          train_jax.py:52-53
+ *   actions[e] = int8(jax.random.randint(action_key, (num_envs_global, n), 0, maxval))[...]       train_jax.py:43-44
+ * action_key == NULL: actions are read from d_actions as in drl_step (then d_actions must not be NULL). */
+int drl_step_keyed(drl_env* env, const uint32_t key[2], const uint32_t action_key[2], int32_t maxval, const void* d_actions,
+                   void* d_rewards, void* d_dones, void* d_obs, void* stream);
+
 /* vmap(env.get_obs)(state, params) -- jax_impl/env/env.py:274-309 (train_jax.py:104,192). */
 int drl_get_obs(drl_env* env, void* d_obs, void* stream);
 

@@ -149,3 +149,36 @@ def test_step_host_pipeline_equals_device_step(N, G, n):
         assert torch.equal(obs.view(torch.int32), d_obs.view(torch.int32))
         if h_obs is not None:
             assert torch.equal(obs.cpu().view(torch.int32), h_obs.view(torch.int32))
+
+
+@pytest.mark.parametrize('G,n,r,N,off,Ng', [(9, 4, 3, 5000, 0, 5000), (8, 3, 3, 3001, 7000, 16001), (11, 20, 1, 300, 50, 400),
+                                            (12, 6, 4, 700, 100, 900), (64, 32, 5, 24, 8, 40)])
+def test_step_keyed_equals_explicit_keys_and_actions(c_oracle, G, n, r, N, off, Ng):
+    """drl_step_keyed hashes split(key, N_global) rows and randint actions inside the step kernel: identical to
+    feeding the same keys and actions as arrays (train_jax.py:43-44,52-54), on a slice of a larger job."""
+    import dronerl_b200 as drl
+    C = c_oracle
+    extra = {'stations_factor': 8, 'skyscrapers_factor': 16} if G == 64 else \
+        {'packets_factor': 1, 'dropzones_factor': 1, 'stations_factor': 1, 'skyscrapers_factor': 1} if n == 20 else {}
+    p = drl.DroneEnvParams(grid_size=G, n_drones=n, window_radius=r, **extra)
+    op = oracle_params(p)
+    env = drl.DeliveryDrones()
+    key0 = drl.random.PRNGKey(11)
+    state = env.reset(key0, p, num_envs=N, env_offset=off, num_envs_global=Ng)
+    ostate = C.reset(C.split(key0, Ng)[off:off + N], op)
+    assert_state_equal(state, ostate, 'reset')
+    rng = np.random.default_rng(1)
+    for t in range(10):
+        k_env, k_act = drl.random.PRNGKey(300 + t), drl.random.PRNGKey(400 + t)
+        keys = C.split(k_env, Ng)[off:off + N]
+        if t % 2 == 0:      # keys and actions both hashed in the kernel
+            acts = C.randint(k_act, Ng * n, 0, 5).reshape(Ng, n)[off:off + N].astype(np.int32)
+            out = env.step(k_env, state, None, p, return_obs=True, action_key=k_act)
+        else:               # keys hashed in the kernel, actions from memory
+            acts = rng.integers(0, 5, size=(N, n)).astype(np.int32)
+            out = env.step(k_env, state, torch.from_numpy(acts).cuda(), p, return_obs=True)
+        orew, odone = C.step(keys, ostate, acts, op)
+        assert_state_equal(out[0], ostate, f'step {t}')
+        np.testing.assert_array_equal(out[1].cpu().numpy().view(np.uint32), orew.view(np.uint32), err_msg=f'rewards {t}')
+        np.testing.assert_array_equal(out[2].cpu().numpy(), odone, err_msg=f'dones {t}')
+        np.testing.assert_array_equal(out[3].cpu().numpy().view(np.uint32), C.get_obs(ostate, op).view(np.uint32), err_msg=f'obs {t}')
