@@ -206,31 +206,45 @@ k_step_fast(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint
     const D d{c};
     const int GS = d.GS(), nvec = GS >> 4, n = d.n();
     __syncthreads();
-    for (long long e = blockIdx.x; e < c.N; e += gridDim.x) {
-        if (e + gridDim.x < c.N) {          // pull the next env's inputs into L2 while this one is stepped
-            const long long en = e + gridDim.x;
-            for (int i = threadIdx.x; i < nvec; i += T) asm volatile("prefetch.global.L2 [%0];" ::"l"(ground + en * GS + 16 * i));
-            if ((int)threadIdx.x < n) asm volatile("prefetch.global.L2 [%0];" ::"l"(drones + en * n + threadIdx.x));
-            if (threadIdx.x == 32) asm volatile("prefetch.global.L2 [%0];" ::"l"(actions + en * n));
-            if (threadIdx.x == 33) asm volatile("prefetch.global.L2 [%0];" ::"l"(keys + 2 * en));
+    // Software pipeline: the next env's first ground vector per thread, drone record and action are loaded into
+    // registers right after the selection phases of the current env (register pressure peaks there, not in the
+    // observation phase that follows), so the loads fly during write-back and tile composition.
+    uint4 nx_gv = make_uint4(0, 0, 0, 0);
+    uint32_t nx_rec = 0;
+    int nx_act = 4;
+    uint2 nx_key = make_uint2(0, 0);
+    auto fetch = [&](long long e) {
+        if (e < c.N) {
+            if (!c.key_mode) nx_key = *reinterpret_cast<const uint2*>(keys + 2 * e);
+            if ((int)threadIdx.x < nvec) nx_gv = reinterpret_cast<const uint4*>(ground + e * GS)[threadIdx.x];
+            if ((int)threadIdx.x < n) {
+                nx_rec = drones[e * n + threadIdx.x];
+                if (!c.act_mode) nx_act = (int)actions[e * n + threadIdx.x];
+            }
         }
+    };
+    fetch(blockIdx.x);
+    for (long long e = blockIdx.x; e < c.N; e += gridDim.x) {
         int zc = 0;
-        for (int i = threadIdx.x; i < nvec; i += T) {
+        if ((int)threadIdx.x < nvec) {
+            reinterpret_cast<uint4*>(sm.sg)[threadIdx.x] = nx_gv;
+            zc = zero_bytes16(nx_gv);
+        }
+        for (int i = threadIdx.x + T; i < nvec; i += T) {       // grids beyond 64x64: the rest of the row
             const uint4 v = reinterpret_cast<const uint4*>(ground + e * GS)[i];
             reinterpret_cast<uint4*>(sm.sg)[i] = v;
             zc += zero_bytes16(v);
         }
-        uint32_t rec = 0;
-        int act = 4;
-        if ((int)threadIdx.x < n) {
-            rec = drones[e * n + threadIdx.x];
-            act = c.act_mode ? derive_action(c, e, (int)threadIdx.x) : (int)actions[e * n + threadIdx.x];
-        }
+        uint32_t rec = nx_rec;
+        int act = nx_act;
+        if (c.act_mode && (int)threadIdx.x < n) act = derive_action(c, e, (int)threadIdx.x);
         if (c.key_mode && warp == 1 && lane < 2) sm.misc[8 + lane] = derive_key_word(c, e, lane);   // published by the barrier below
+        const uint2 key_e = nx_key;
         const int F0 = grp.sum(zc) - (GS - d.G2());
-        const uint2 kk = c.key_mode ? make_uint2(sm.misc[8], sm.misc[9]) : *reinterpret_cast<const uint2*>(keys + 2 * e);
+        const uint2 kk = c.key_mode ? make_uint2(sm.misc[8], sm.misc[9]) : key_e;
         const Stats before = st;
         const bool ok = env_step_fast<T, NB>(grp, c, d, sm, sel, F0, rec, act, kk.x, kk.y, rewards + e * n, dones + e * n, st);
+        fetch(e + gridDim.x);
         if (ok) {
             for (int i = threadIdx.x; i < nvec; i += T)
                 reinterpret_cast<uint4*>(ground + e * GS)[i] = reinterpret_cast<const uint4*>(sm.sg)[i];
