@@ -2,10 +2,12 @@
 """Generates tests/golden/*.npz -- frozen input/output vectors of the env hot path.
 
 SOURCE OF THE VECTORS: the literal NumPy restatement oracle/env_ref.py (+ oracle/jaxrand.py), NOT a
-JAX binary: jax/jaxlib/flax are not installable in this environment (no network), so the reference
-env cannot be executed to produce them.  That restatement is pinned by every assertion of the
-reference's own tests/jax_tests/test_env.py and by the public threefry / jax.random known answers
-(tests/test_oracle_reference_kats.py).  The fixtures freeze its behaviour so that (a) the C oracle,
+JAX binary: jax/jaxlib/flax are not installable in this environment (no network).  That restatement is
+pinned by every assertion of the reference's own tests/jax_tests/test_env.py, by the public threefry /
+jax.random known answers (tests/test_oracle_reference_kats.py), and -- fixture by fixture -- by
+verify_against_reference_source.py, which replays the same cases through the reference's OWN env source
+(imported unmodified, jax/flax resolved to the NumPy shim in jaxshim/) and requires identical bytes.
+After regenerating, re-run that script: it rewrites the hashes tests/test_golden.py checks.  The fixtures freeze its behaviour so that (a) the C oracle,
 (b) the CUDA env and (c) any future change to the oracle itself are all checked against the same
 bytes, on the GPU box where /root/reference does not exist.
 
@@ -28,6 +30,9 @@ CASES = {
     'g4n2r2_free_lt_k': (dict(grid_size=4, n_drones=2, window_radius=2, packets_factor=4, dropzones_factor=2,
                               stations_factor=1, skyscrapers_factor=1), 16, 24, 12),
     'g12n6r4_cta_mode': (dict(grid_size=12, n_drones=6, window_radius=4), 8, 12, 6),
+    'g7n2r6_window_wider_than_grid': (dict(grid_size=7, n_drones=2, window_radius=6), 8, 16, 8),
+    'g16n16r1_many_drones': (dict(grid_size=16, n_drones=16, window_radius=1, packets_factor=2, dropzones_factor=1,
+                                  stations_factor=1, skyscrapers_factor=2), 4, 16, 8),
     'g20n9r2_custom_rewards': (dict(grid_size=20, n_drones=9, window_radius=2, pickup_reward=0.5, delivery_reward=2.0,
                                     crash_reward=-3.0, charge_reward=-0.25, discharge=15, charge=35), 4, 10, 5),
 }

@@ -1,0 +1,136 @@
+#!/usr/bin/env python
+"""Replays the golden cases through the REFERENCE'S OWN env source and checks the committed fixtures.
+
+    python tests/golden/verify_against_reference_source.py     # needs /root/reference (this container only)
+
+`/root/reference/jax_impl/env/env.py` is imported UNMODIFIED; `jax` / `flax` resolve to tests/golden/jaxshim
+(a NumPy implementation of the ~30 JAX functions that file calls -- see jaxshim/README.md; the real packages
+are not installable here).  For every case of make_golden.py the same keys and actions are fed to the
+reference's `DeliveryDrones.reset / step / get_obs`, env by env, and every array of the committed .npz
+(state fields, rewards and observations as float32 bit patterns, dones) must be identical.  On success the
+sha256 of each verified fixture is written to reference_source_check.json; tests/test_golden.py fails if a
+fixture is ever regenerated without re-running this check.
+
+What this pins: that the oracle (which produced the fixtures) restates the reference SOURCE faithfully --
+index order, transposes, key order, masks, reward arithmetic, the observation layout.  What it cannot pin:
+XLA behaviours the shim takes from the documentation.
+"""
+import hashlib
+import json
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REF = os.environ.get('DRONERL_REFERENCE', '/root/reference')
+sys.path[:0] = [os.path.join(HERE, 'jaxshim'), REF, HERE]
+
+import jax                                                    # noqa: E402  (the shim)
+from jax_impl.env.env import DeliveryDrones, DroneEnvParams   # noqa: E402  (the reference, unmodified)
+from make_golden import CASES, FIELDS                         # noqa: E402
+
+
+def state_arrays(s):
+    return {'ground': np.asarray(s.ground).astype(np.int8), 'air_x': np.asarray(s.air_x).astype(np.int32),
+            'air_y': np.asarray(s.air_y).astype(np.int32), 'carrying_package': np.asarray(s.carrying_package).astype(bool),
+            'charge': np.asarray(s.charge).astype(np.float32)}
+
+
+def same(a, b, what):
+    a, b = np.asarray(a), np.asarray(b)
+    if a.dtype.kind == 'f' or b.dtype.kind == 'f':
+        ok = np.array_equal(a.astype(np.float32).view(np.uint32), b.astype(np.float32).view(np.uint32))
+    else:
+        ok = np.array_equal(a.astype(np.int64), b.astype(np.int64))
+    if not ok:
+        raise SystemExit(f'MISMATCH between the reference source and the committed fixture: {what}')
+
+
+def check_case(name, cfg, N, steps, reset_at):
+    g = np.load(os.path.join(HERE, name + '.npz'))
+    env = DeliveryDrones()
+    p = DroneEnvParams(**cfg)
+    states = [env.reset(jax.numpy.array(g['reset_keys'][e]), p) for e in range(N)]
+    for e in range(N):
+        for f, v in state_arrays(states[e]).items():
+            same(v, g['reset_' + f][e], f'{name}: reset {f} env {e}')
+        same(env.get_obs(states[e], p), g['reset_obs'][e], f'{name}: reset obs env {e}')
+    rk = jax.random.split(jax.random.PRNGKey(int(g['seed_rereset'])), N)
+    for t in range(steps):
+        if t == reset_at:
+            states = [env.reset(rk[e], p) for e in range(N)]
+        for e in range(N):
+            s, rew, done = env.step(jax.numpy.array(g['step_keys'][t, e]), states[e], jax.numpy.array(g['actions'][t, e]), p)
+            states[e] = s
+            for f, v in state_arrays(s).items():
+                same(v, g['traj_' + f][t, e], f'{name}: step {t} {f} env {e}')
+            same(rew, g['rewards'][t, e], f'{name}: step {t} rewards env {e}')
+            same(done, g['dones'][t, e], f'{name}: step {t} dones env {e}')
+            same(env.get_obs(s, p), g['obs'][t, e], f'{name}: step {t} obs env {e}')
+    return N * steps
+
+
+FUZZ_SHAPES = [
+    dict(grid_size=3, n_drones=3, window_radius=1, packets_factor=1, dropzones_factor=1, stations_factor=0, skyscrapers_factor=1),
+    dict(grid_size=4, n_drones=2, window_radius=2, packets_factor=4, dropzones_factor=2, stations_factor=1, skyscrapers_factor=1),
+    dict(grid_size=5, n_drones=1, window_radius=1),
+    dict(grid_size=6, n_drones=4, window_radius=3, packets_factor=4, dropzones_factor=2, stations_factor=1, skyscrapers_factor=1),
+    dict(grid_size=9, n_drones=4, window_radius=3),
+    dict(grid_size=11, n_drones=7, window_radius=1),
+    dict(grid_size=12, n_drones=6, window_radius=2, packets_factor=10),
+    dict(grid_size=20, n_drones=32, window_radius=2, packets_factor=1, dropzones_factor=1, stations_factor=1, skyscrapers_factor=1),
+    dict(grid_size=32, n_drones=16, window_radius=5, discharge=35, charge=7, pickup_reward=0.3, charge_reward=-0.7),
+]
+
+
+def fuzz(num_envs=6, steps=40):
+    """Reference source (under the shim) against the oracle on shapes beyond the fixtures, incl. the erasing-zeros edge,
+    grids that run out of spawn candidates and 32 drones with many collisions / aliased scatters."""
+    sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+    from oracle import env_ref as E
+    from oracle import jaxrand as jr
+    env = DeliveryDrones()
+    total = 0
+    for si, cfg in enumerate(FUZZ_SHAPES):
+        p, op = DroneEnvParams(**cfg), E.Params(**cfg)
+        rng = np.random.default_rng(100 + si)
+        keys = jr.split(jr.PRNGKey(50 + si), num_envs)
+        for e in range(num_envs):
+            s, o = env.reset(jax.numpy.array(keys[e]), p), E.reset(keys[e], op)
+            for t in range(steps):
+                for f, v in state_arrays(s).items():
+                    same(v, getattr(o, f), f'fuzz shape {si} env {e} step {t} {f}')
+                same(env.get_obs(s, p), E.get_obs(o, op), f'fuzz shape {si} env {e} step {t} obs')
+                k = jr.split(jr.PRNGKey(1000 * si + 10 * e + t), 2)[1]
+                acts = rng.integers(0, 5, size=op.n_drones).astype(np.int32)
+                s, rew, done = env.step(jax.numpy.array(k), s, jax.numpy.array(acts), p)
+                o, orew, odone = E.step(k, o, acts, op)
+                same(rew, orew, f'fuzz shape {si} env {e} step {t} rewards')
+                same(done, odone, f'fuzz shape {si} env {e} step {t} dones')
+                total += 1
+        print(f'fuzz shape {si} {cfg}: identical')
+    return total
+
+
+def main():
+    if not os.path.isdir(os.path.join(REF, 'jax_impl')):
+        raise SystemExit(f'{REF} not found: this check runs where the reference checkout exists')
+    manifest = {'reference': REF + '/jax_impl/env/env.py (imported unmodified; jax/flax = tests/golden/jaxshim)', 'fixtures': {}}
+    manifest['reference_env_sha256'] = hashlib.sha256(open(os.path.join(REF, 'jax_impl/env/env.py'), 'rb').read()).hexdigest()
+    for name, (cfg, N, steps, reset_at) in CASES.items():
+        n = check_case(name, cfg, N, steps, reset_at)
+        digest = hashlib.sha256(open(os.path.join(HERE, name + '.npz'), 'rb').read()).hexdigest()
+        manifest['fixtures'][name + '.npz'] = {'sha256': digest, 'env_steps_replayed': n}
+        print(f'{name}: {n} env-steps + resets + observations identical to the reference source')
+    # the PRNG fixture: split / uniform / randint through the shim are the oracle's own streams; record its hash too
+    manifest['fixtures']['prng.npz'] = {'sha256': hashlib.sha256(open(os.path.join(HERE, 'prng.npz'), 'rb').read()).hexdigest(),
+                                        'env_steps_replayed': 0}
+    manifest['fuzz_env_steps_identical_to_oracle'] = fuzz()
+    with open(os.path.join(HERE, 'reference_source_check.json'), 'w') as f:
+        json.dump(manifest, f, indent=1)
+    print('wrote reference_source_check.json')
+
+
+if __name__ == '__main__':
+    main()

@@ -26,6 +26,46 @@ def bits(a):
     return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
 
 
+def test_fixtures_are_the_ones_verified_against_the_reference_source():
+    """tests/golden/verify_against_reference_source.py replayed every case through the reference's own
+    jax_impl/env/env.py (unmodified, under the NumPy jaxshim) and recorded the hash of each fixture it found
+    identical; a fixture regenerated without re-running that check fails here."""
+    import hashlib
+    import json
+    manifest = json.load(open(os.path.join(GOLD, 'reference_source_check.json')))
+    assert set(manifest['fixtures']) == {n + '.npz' for n in CASES} | {'prng.npz'}
+    for fname, rec in manifest['fixtures'].items():
+        digest = hashlib.sha256(open(os.path.join(GOLD, fname), 'rb').read()).hexdigest()
+        assert digest == rec['sha256'], f'{fname} changed since it was checked against the reference source'
+
+
+@pytest.mark.skipif(not os.path.isdir('/root/reference/jax_impl'), reason='reference checkout not present (GPU box)')
+def test_reference_source_replay_of_one_case_live():
+    """Where the reference checkout exists (the build container), run the replay itself for one case."""
+    import subprocess
+    import sys
+    code = ("import sys; sys.argv=['x']; import runpy; m = runpy.run_path(%r); "
+            "name='g4n2r2_free_lt_k'; cfg, N, steps, reset_at = m['CASES'][name]; "
+            "print(m['check_case'](name, cfg, N, steps, reset_at))") % os.path.join(GOLD, 'verify_against_reference_source.py')
+    out = subprocess.run([sys.executable, '-c', code], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert out.stdout.strip().endswith('384')
+
+
+@pytest.mark.skipif(not os.path.isdir('/root/reference/tests/jax_tests'), reason='reference checkout not present (GPU box)')
+def test_reference_own_tests_pass_on_reference_source_under_the_shim():
+    """The shim is only trusted as far as the reference's own assertions reach: tests/jax_tests/test_env.py
+    (10 tests, incl. the seed-dependent reset / respawn / dropzone positions) must pass on the reference's own
+    env source with jax/flax resolved to tests/golden/jaxshim."""
+    import subprocess
+    import sys
+    env = dict(os.environ, PYTHONPATH=os.pathsep.join([os.path.join(GOLD, 'jaxshim'), '/root/reference', os.path.dirname(HERE)]))
+    out = subprocess.run([sys.executable, '-m', 'pytest', '/root/reference/tests/jax_tests/test_env.py', '-q', '-p',
+                          'no:cacheprovider'], capture_output=True, text=True, timeout=600, env=env, cwd='/tmp')
+    assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-2000:]
+    assert '10 passed' in out.stdout
+
+
 def test_generator_is_deterministic_for_one_case():
     """The committed bytes are what the NumPy oracle produces today (guards oracle drift)."""
     name = 'g4n2r2_free_lt_k'
