@@ -928,8 +928,10 @@ int drl_step_host(drl_env* env, const uint32_t key[2], const int8_t* h_actions, 
     CUDA_TRY(env, cudaEventRecord(env->pipe_begin, s));
     // chunks of a whole number of 1024-env blocks: H2D actions -> step+obs -> D2H rewards, dones (, obs)
     const long long kMinChunk = 32768;
+    int max_chunks = 8;
+    if (const char* hc = getenv("DRL_HOST_CHUNKS")) max_chunks = atoi(hc) < 1 ? 1 : atoi(hc) > 15 ? 15 : atoi(hc);   // A/B switch
     int chunks = (int)(c.N / kMinChunk);
-    chunks = chunks < 1 ? 1 : chunks > 8 ? 8 : chunks;
+    chunks = chunks < 1 ? 1 : chunks > max_chunks ? max_chunks : chunks;
     const long long per = ((c.N + chunks - 1) / chunks + 1023) / 1024 * 1024;
     const long long obs_env = (long long)c.obs_n * c.W2 * 6;     // floats per env
     int used = 0;
