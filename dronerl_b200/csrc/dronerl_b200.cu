@@ -179,10 +179,10 @@ k_step_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint3
 // Fast path of the CTA-mode step (see env_step_fast): TF threads per env, nothing of a noise vector kept in
 // registers.  Envs it cannot finish are appended to ``redo`` untouched and stepped by k_step_cta right after.
 #ifndef DRL_FAST_THREADS
-#define DRL_FAST_THREADS 256
+#define DRL_FAST_THREADS 128
 #endif
 #ifndef DRL_FAST_MIN_BLOCKS
-#define DRL_FAST_MIN_BLOCKS 4
+#define DRL_FAST_MIN_BLOCKS 7
 #endif
 constexpr int kFastThreads = DRL_FAST_THREADS;
 
@@ -412,9 +412,10 @@ static void carve_layout(DevCfg& c, bool warp_mode, int Q, bool fast, int cta_th
     c.off_red = c.off_misc + 48;
     c.off_sel = round_up(c.off_red + (warp_mode ? 0 : 2 * (cta_threads / 32) * 8), 16);
     c.sel_hist = fast ? 0 : 1024;
-    c.sel_cap = fast ? 384 : c.sel_maxj + 256;      // J keys plus a generous few histogram bins' worth (fast: 128 keys + 256 parked)
+    c.sel_cap = fast ? 256 : c.sel_maxj + 256;      // J keys plus a generous few histogram bins' worth (fast: 128 keys + 128 parked)
     // CTA mode only: histogram [256] | counters [4] | key list [cap] | rank -> position table [maxj]
-    const int sel_bytes = warp_mode ? 0 : c.sel_hist + 32 + c.sel_cap * 8 + round_up(c.sel_maxj * 2, 16);
+    // the fast kernel ranks at most n <= 32 drones' worth of positions
+    const int sel_bytes = warp_mode ? 0 : c.sel_hist + 32 + c.sel_cap * 8 + round_up((fast ? 64 : c.sel_maxj) * 2, 16);
     c.off_tile = round_up(c.off_sel + sel_bytes, 128);
     c.group_bytes = c.off_tile + c.tile_bufs * c.tile_stride * (warp_mode ? 1 : cta_threads / 32);
 }
@@ -457,17 +458,15 @@ static const void* pick_step(const drl_env* e) {
 // Fast CTA-mode kernel of this shape (nullptr: none -- warp mode, or switched off with DRL_NO_FAST=1 for A/B runs).
 static int fast_nb(const drl_env* e) {
     const int H = e->dc.H;
-    return H <= 2 * kFastThreads ? 2 : H <= 4 * kFastThreads ? 4 : H <= 8 * kFastThreads ? 8 : H <= 16 * kFastThreads ? 16 : 0;
+    // (the fast kernel loops over its blocks at run time; the count only picks how many are hashed together)
+    return H <= 2 * kFastThreads ? 2 : 4;
 }
 static const void* pick_fast(const drl_env* e) {
     if (e->warp_mode || !e->use_fast) return nullptr;
-    if (static_shape(e) == 3) return (const void*)k_step_fast<(64 * 64 / 2) / kFastThreads, DLW>;
+    if (static_shape(e) == 3) return (const void*)k_step_fast<4, DLW>;
     switch (fast_nb(e)) {
         case 2: return (const void*)k_step_fast<2, DynDims>;
-        case 4: return (const void*)k_step_fast<4, DynDims>;
-        case 8: return (const void*)k_step_fast<8, DynDims>;
-        case 16: return (const void*)k_step_fast<16, DynDims>;
-        default: return nullptr;
+        default: return (const void*)k_step_fast<4, DynDims>;
     }
 }
 static reset_fn pick_reset(const drl_env* e) {

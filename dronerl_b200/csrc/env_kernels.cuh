@@ -1019,8 +1019,8 @@ __device__ __forceinline__ bool env_step_fast(Group<T>& grp, const DevCfg& c, co
     const int tid = threadIdx.x, lane = threadIdx.x & 31;
     const bool drone_warp = threadIdx.x < 32;
     const int G = d.G(), G2 = d.G2(), n = d.n();
-    uint2* const stage_air = reinterpret_cast<uint2*>(sel.list + 256);
-    uint32_t* const nstage_air = sel.cnt + 4;
+    uint2* const stage_air = reinterpret_cast<uint2*>(sel.list + 128);     // the ground spawns are done with it by then
+    uint32_t* const nstage_air = sel.cnt + 3;
     const int ncand_air = G2 - 1 - c.k_reset[3] - n;        // estimate: cells minus skyscrapers, survivors, the last cell
     DroneOut o;
     uint32_t sk0 = 0, sk1 = 0, rk0 = 0, rk1 = 0;
