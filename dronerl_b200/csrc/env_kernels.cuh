@@ -919,8 +919,7 @@ __device__ __forceinline__ void env_step(Group<T>& grp, const DevCfg& c, const D
 // and the env is stepped again by the general kernel from its untouched state (redo list).
 // Pre-filter threshold on the raw 32-bit words for J winners among about ``ncand`` candidates.
 __device__ __forceinline__ uint32_t select_threshold(int J, int ncand) {
-    int sq = 1;
-    while (sq * sq < J) ++sq;
+    const int sq = (int)ceilf(sqrtf((float)J));
     const int target = J + 4 * sq + 8;                      // <= 64 for J <= 32
     uint32_t T0 = 0;
     if (ncand > target) T0 = (uint32_t)(8388608.0f * (1.0f - __fdividef((float)target, (float)ncand)));
@@ -938,6 +937,8 @@ __device__ __forceinline__ void park_pass(const D& d, int worker, int count, uin
         const uint32_t i = atomicAdd(nstage, 1u);
         if (i < 128u) stage[i] = make_uint2(o, (uint32_t)cell);
     };
+    // when the workers tile the blocks exactly (and the vector has no pad counter) the bounds checks fold away
+    const bool exact = H % (count * CH) == 0 && 2 * H == G2;
 #pragma unroll 1
     for (int b0 = worker; b0 < H; b0 += count * CH) {
         uint32_t x0[CH], x1[CH];
@@ -945,14 +946,14 @@ __device__ __forceinline__ void park_pass(const D& d, int worker, int count, uin
         for (int t = 0; t < CH; ++t) {
             const int b = b0 + t * count, hi = H + b;
             x0[t] = (uint32_t)b;
-            x1[t] = hi < G2 ? (uint32_t)hi : 0u;
+            x1[t] = (exact || hi < G2) ? (uint32_t)hi : 0u;
         }
         drl_threefry2x32_n<CH>(k0, k1, x0, x1);
 #pragma unroll
         for (int t = 0; t < CH; ++t) {
             const int b = b0 + t * count;
-            if (x0[t] >= T0s && b < H) park(x0[t], b);
-            if (x1[t] >= T0s && b < H && H + b < G2) park(x1[t], H + b);
+            if (x0[t] >= T0s && (exact || b < H)) park(x0[t], b);
+            if (x1[t] >= T0s && (exact || (b < H && H + b < G2))) park(x1[t], H + b);
         }
     }
 }
