@@ -32,7 +32,7 @@ for w in RAW:
         vals = [r[i] for r in rows[1:]]
         print(f'{w:70s} {vals}')
         if w == 'smsp__inst_executed.sum':
-            inst = float(vals[-1].replace(',', ''))
+            inst = max(float(v.replace(',', '')) for v in vals[1:])   # the dominant kernel of the capture
 if inst:
     print(f'warp-instructions per env: {inst / nenv:.0f}')
 
