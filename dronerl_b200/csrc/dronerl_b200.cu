@@ -49,13 +49,14 @@ template <int NB, int Q, class D>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32, DRL_STEP_MIN_BLOCKS)
 k_step_warp(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint32_t* __restrict__ drones,
             const uint32_t* __restrict__ keys, const int8_t* __restrict__ actions, float* __restrict__ rewards,
-            uint8_t* __restrict__ dones, float* __restrict__ obs, unsigned long long* __restrict__ stats) {
+            uint8_t* __restrict__ dones, float* __restrict__ obs, unsigned long long* __restrict__ stats,
+            unsigned* __restrict__ queue) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5;
     const D d{c};
     step_warp_body<NB, Q, D>(c, d, smem_raw + (size_t)warp * c.group_bytes, ground, drones, keys, actions, rewards, dones,
                              obs, stats, (long long)blockIdx.x * kWarpsPerBlock + warp,
-                             (long long)gridDim.x * kWarpsPerBlock);
+                             (long long)gridDim.x * kWarpsPerBlock, queue);
 }
 
 template <int NB>
@@ -190,7 +191,8 @@ template <int NB, class D>
 __global__ void __launch_bounds__(kFastThreads, DRL_FAST_MIN_BLOCKS)
 k_step_fast(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint32_t* __restrict__ drones,
             const uint32_t* __restrict__ keys, const int8_t* __restrict__ actions, float* __restrict__ rewards,
-            uint8_t* __restrict__ dones, float* __restrict__ obs, unsigned long long* __restrict__ stats, int* redo, int* redo_list) {
+            uint8_t* __restrict__ dones, float* __restrict__ obs, unsigned long long* __restrict__ stats, int* redo, int* redo_list,
+            unsigned* __restrict__ queue) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     constexpr int T = kFastThreads;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -224,7 +226,16 @@ k_step_fast(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint
         }
     };
     fetch(blockIdx.x);
-    for (long long e = blockIdx.x; e < c.N; e += gridDim.x) {
+    // Env order: after its first env a CTA draws the next one from a device-wide ticket counter (time order keeps
+    // the obs stream's DRAM locality, see step_warp.cuh); queue == nullptr: static grid-stride order.
+    long long en = 0;
+    unsigned tk = 0;                                        // thread 0: the ticket drawn one env ahead
+    if (queue != nullptr && threadIdx.x == 0) tk = atomicAdd(queue, 1u);
+    for (long long e = blockIdx.x; e < c.N; e = en) {
+        if (queue != nullptr && threadIdx.x == 0) {
+            sm.misc[10] = tk;                               // published by the barrier in grp.sum
+            tk = atomicAdd(queue, 1u);                      // in flight while this env is stepped
+        }
         int zc = 0;
         if ((int)threadIdx.x < nvec) {
             reinterpret_cast<uint4*>(sm.sg)[threadIdx.x] = nx_gv;
@@ -242,9 +253,10 @@ k_step_fast(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint
         const uint2 key_e = nx_key;
         const int F0 = grp.sum(zc) - (GS - d.G2());
         const uint2 kk = c.key_mode ? make_uint2(sm.misc[8], sm.misc[9]) : key_e;
+        en = queue != nullptr ? (long long)gridDim.x + (long long)sm.misc[10] : e + gridDim.x;
         const Stats before = st;
         const bool ok = env_step_fast<T, NB>(grp, c, d, sm, sel, F0, rec, act, kk.x, kk.y, rewards + e * n, dones + e * n, st);
-        fetch(e + gridDim.x);
+        fetch(en);
         if (ok) {
             for (int i = threadIdx.x; i < nvec; i += T)
                 reinterpret_cast<uint4*>(ground + e * GS)[i] = reinterpret_cast<const uint4*>(sm.sg)[i];
@@ -263,6 +275,13 @@ k_step_fast(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint
     }
     tile_drain(lane);
     if (warp == 0) flush_stats(st, env_steps, stats, lane);
+    if (queue != nullptr && threadIdx.x == 0) {
+        __threadfence();                                    // the last ticket drawn is ordered before the exit count
+        if (atomicAdd(queue + 1, 1u) == gridDim.x - 1u) {
+            queue[0] = 0u;                                  // every CTA has drawn its last ticket by now
+            queue[1] = 0u;
+        }
+    }
 }
 
 template <int NB>
@@ -379,6 +398,7 @@ struct drl_env {
     int per_sm_step;      // resident step CTAs per SM (grid sizing of chunk launches)
     int use_fast;         // CTA mode: run the streamed-selection kernel first, the general one on its redo list
     int per_sm_fast;
+    int static_order;     // A/B: step kernels walk the envs in grid-stride order instead of drawing tickets
     DevCfg fast_dc;       // the fast kernel's shared-memory layout (otherwise equal to dc)
     int* d_redo;          // [64] headers (4 ints per concurrent launch slot) + [N] redo list
     int smem_optin;       // device limit of opt-in dynamic shared memory per CTA
@@ -579,12 +599,14 @@ static int launch_step(drl_env* env, long long first, long long count, const uin
     float* rewards = d_rewards + first * n;
     uint8_t* dones = d_dones + first * n;
     float* obs = d_obs ? d_obs + first * dc.obs_n * dc.W2 * 6 : nullptr;
+    // ticket counters of this launch slot (tickets drawn, workers finished); the last worker out re-arms them
+    unsigned* queue = env->static_order ? nullptr : reinterpret_cast<unsigned*>(env->d_stats + DRL_NUM_STATS + 2) + 2 * slot;
     if (env->warp_mode) {
         const long long per_cta = (long long)kWarpsPerBlock * env->envs_per_warp;
         const long long units = (count + per_cta - 1) / per_cta, resident = (long long)env->per_sm_step * env->sm_count;
         if (launches) *launches += 1;
         return launch(env, "step kernel", pick_step(env), (int)(units < resident ? units : resident), kWarpsPerBlock * 32,
-                      env->smem_bytes, (void*)s, dc, ground, drones, keys, actions, rewards, dones, obs, env->d_stats);
+                      env->smem_bytes, (void*)s, dc, ground, drones, keys, actions, rewards, dones, obs, env->d_stats, queue);
     }
     const long long resident = (long long)env->per_sm_step * env->sm_count;
     const int grid_slow = (int)(count < resident ? count : resident);
@@ -600,7 +622,7 @@ static int launch_step(drl_env* env, long long first, long long count, const uin
         fdc.ntiles = dc.ntiles;
         fill_derivation(env, fdc, first, sk);
         int rc = launch(env, "fast step kernel", ff, (int)(count < rf ? count : rf), kFastThreads, fdc.group_bytes, (void*)s, fdc,
-                        ground, drones, keys, actions, rewards, dones, obs, env->d_stats, hdr, list);
+                        ground, drones, keys, actions, rewards, dones, obs, env->d_stats, hdr, list, queue);
         if (rc) return rc;
         if (launches) *launches += 1;
     }
@@ -706,6 +728,8 @@ int drl_create(const drl_config* cfg, drl_env** out) {
 
     e->smem_optin = (int)prop.sharedMemPerBlockOptin;
     {
+        const char* so = getenv("DRL_STATIC_ORDER");     // A/B switch: static grid-stride env order in the step kernels
+        e->static_order = so && so[0] == '1';
         const char* nf = getenv("DRL_NO_FAST");          // A/B switch: general CTA kernel only
         e->use_fast = !e->warp_mode && !(nf && nf[0] == '1') && n <= 32;
     }
@@ -715,8 +739,9 @@ int drl_create(const drl_config* cfg, drl_env** out) {
         return DRL_ECUDA;
     }
     // statistics block + 16 bytes of key scratch for the *_dev entry points
-    if (cudaMalloc(&e->d_stats, (DRL_NUM_STATS + 2) * sizeof(unsigned long long)) != cudaSuccess ||
-        cudaMemset(e->d_stats, 0, DRL_NUM_STATS * sizeof(unsigned long long)) != cudaSuccess) {
+    // + 16 ticket-counter pairs (one per concurrent launch slot) for the step kernels' dynamic env order
+    if (cudaMalloc(&e->d_stats, (DRL_NUM_STATS + 2 + 16) * sizeof(unsigned long long)) != cudaSuccess ||
+        cudaMemset(e->d_stats, 0, (DRL_NUM_STATS + 2 + 16) * sizeof(unsigned long long)) != cudaSuccess) {
         delete e;
         return fail(nullptr, DRL_ECUDA, "cudaMalloc of the statistics block failed%s");
     }
