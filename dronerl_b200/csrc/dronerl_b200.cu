@@ -1,5 +1,6 @@
 // dronerl_b200: kernels + C ABI (include/dronerl_b200.h) of the batched DroneRL env for sm_100a.
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -shared -Xcompiler -fPIC
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -45,7 +46,7 @@ __device__ __forceinline__ void zero_code(const DevCfg& c, const Smem& sm, int t
 
 // ---- warp-per-env kernels (grids up to 128 cells) ---------------------------------------------
 
-template <int NB, int Q, class D>
+template <int NB, int Q, class D, bool HP = false>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32, DRL_STEP_MIN_BLOCKS)
 k_step_warp(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint32_t* __restrict__ drones,
             const uint32_t* __restrict__ keys, const int8_t* __restrict__ actions, float* __restrict__ rewards,
@@ -54,7 +55,7 @@ k_step_warp(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5;
     const D d{c};
-    step_warp_body<NB, Q, D>(c, d, smem_raw + (size_t)warp * c.group_bytes, ground, drones, keys, actions, rewards, dones,
+    step_warp_body<NB, Q, D, HP>(c, d, smem_raw + (size_t)warp * c.group_bytes, ground, drones, keys, actions, rewards, dones,
                              obs, stats, (long long)blockIdx.x * kWarpsPerBlock + warp,
                              (long long)gridDim.x * kWarpsPerBlock, queue);
 }
@@ -399,6 +400,8 @@ struct drl_env {
     int use_fast;         // CTA mode: run the streamed-selection kernel first, the general one on its redo list
     int per_sm_fast;
     int static_order;     // A/B: step kernels walk the envs in grid-stride order instead of drawing tickets
+    unsigned* d_chunk_done;   // drl_step_host, single-launch pipeline: envs finished per chunk (64 counters) + 64 input flags
+    unsigned host_epoch;      // ... value the input flags of the current call are set to
     DevCfg fast_dc;       // the fast kernel's shared-memory layout (otherwise equal to dc)
     int* d_redo;          // [64] headers (4 ints per concurrent launch slot) + [N] redo list
     int smem_optin;       // device limit of opt-in dynamic shared memory per CTA
@@ -475,6 +478,15 @@ static const void* pick_step(const drl_env* e) {
     return e->nb == 2 ? (const void*)k_step_cta<2, DynDims> : e->nb == 4 ? (const void*)k_step_cta<4, DynDims>
          : e->nb == 8 ? (const void*)k_step_cta<8, DynDims> : (const void*)k_step_cta<16, DynDims>;
 }
+// Warp-mode instance with drl_step_host's pipeline hooks (static shapes only; nullptr: use one launch per chunk).
+static const void* pick_step_hostpipe(const drl_env* e) {
+    if (!e->warp_mode) return nullptr;
+    switch (static_shape(e)) {
+        case 1: return (const void*)k_step_warp<2, DRL_QMAX, D943, true>;
+        case 2: return (const void*)k_step_warp<1, DRL_QMAX, D833, true>;
+        default: return nullptr;
+    }
+}
 // Fast CTA-mode kernel of this shape (nullptr: none -- warp mode, or switched off with DRL_NO_FAST=1 for A/B runs).
 static int fast_nb(const drl_env* e) {
     const int H = e->dc.H;
@@ -528,6 +540,10 @@ static int configure_launches(drl_env* e) {
     const DevCfg& c = e->dc;
     const int Q = e->envs_per_warp;
     const int threads = e->warp_mode ? kWarpsPerBlock * 32 : kCtaThreads;
+    if (const void* hp = pick_step_hostpipe(e)) {
+        if (cudaFuncSetAttribute(hp, cudaFuncAttributeMaxDynamicSharedMemorySize, e->smem_optin) != cudaSuccess)
+            return fail(e, DRL_ECUDA, "kernel setup failed (host-pipeline step instance)%s");
+    }
     const void* fns[3] = {pick_step(e), (const void*)pick_reset(e), (const void*)pick_obs(e)};
     int* grids[3] = {&e->grid_step, &e->grid_reset, &e->grid_obs};
     for (int i = 0; i < 3; ++i) {
@@ -587,9 +603,17 @@ static void fill_derivation(const drl_env* env, DevCfg& dc, long long first, con
 
 static int launch_step(drl_env* env, long long first, long long count, const uint32_t* d_keys, const int8_t* d_actions,
                        float* d_rewards, uint8_t* d_dones, float* d_obs, cudaStream_t s, int slot, int* launches,
-                       const StepKeys* sk = nullptr) {
+                       const StepKeys* sk = nullptr, int grid_pct = 100, unsigned* chunk_done = nullptr, int chunk_shift = 0,
+                       const unsigned* chunk_in = nullptr, unsigned in_epoch = 0) {
+    // grid_pct < 100: launch on that share of the resident CTA count, so that chunk launches on two streams run side
+    // by side (with ticketed env order every worker of a launch finishes at the same moment; a full-size grid would
+    // leave the next chunk's start-up and this chunk's tail exposed at every boundary)
     DevCfg dc = env->dc;
     dc.N = count;
+    dc.chunk_done = chunk_done;
+    dc.chunk_shift = chunk_shift;
+    dc.chunk_in = chunk_in;
+    dc.in_epoch = in_epoch;
     fill_derivation(env, dc, first, sk);
     const long long n = dc.n;
     uint8_t* ground = env->d_ground + first * dc.GS;
@@ -603,9 +627,12 @@ static int launch_step(drl_env* env, long long first, long long count, const uin
     unsigned* queue = env->static_order ? nullptr : reinterpret_cast<unsigned*>(env->d_stats + DRL_NUM_STATS + 2) + 2 * slot;
     if (env->warp_mode) {
         const long long per_cta = (long long)kWarpsPerBlock * env->envs_per_warp;
-        const long long units = (count + per_cta - 1) / per_cta, resident = (long long)env->per_sm_step * env->sm_count;
+        const long long units = (count + per_cta - 1) / per_cta;
+        long long resident = (long long)env->per_sm_step * env->sm_count * grid_pct / 100;
+        resident = resident < 1 ? 1 : resident;
         if (launches) *launches += 1;
-        return launch(env, "step kernel", pick_step(env), (int)(units < resident ? units : resident), kWarpsPerBlock * 32,
+        const void* fn = chunk_done != nullptr ? pick_step_hostpipe(env) : pick_step(env);
+        return launch(env, "step kernel", fn, (int)(units < resident ? units : resident), kWarpsPerBlock * 32,
                       env->smem_bytes, (void*)s, dc, ground, drones, keys, actions, rewards, dones, obs, env->d_stats, queue);
     }
     const long long resident = (long long)env->per_sm_step * env->sm_count;
@@ -615,7 +642,8 @@ static int launch_step(drl_env* env, long long first, long long count, const uin
     if (const void* ff = pick_fast(env)) {
         hdr = env->d_redo + 4 * slot;
         list = env->d_redo + 64 + first;
-        const long long rf = (long long)env->per_sm_fast * env->sm_count;
+        long long rf = (long long)env->per_sm_fast * env->sm_count * grid_pct / 100;
+        rf = rf < 1 ? 1 : rf;
         DevCfg fdc = env->fast_dc;
         fdc.N = count;
         fdc.obs_n = dc.obs_n;
@@ -766,6 +794,7 @@ void drl_destroy(drl_env* env) {
     cudaFree(env->s_actions);
     cudaFree(env->s_rewards);
     cudaFree(env->s_dones);
+    cudaFree(env->d_chunk_done);
     for (int i = 0; i < 2; ++i) {
         if (env->pipe_stream[i]) cudaStreamDestroy(env->pipe_stream[i]);
         if (env->pipe_end[i]) cudaEventDestroy(env->pipe_end[i]);
@@ -928,11 +957,86 @@ static int ensure_scratch(drl_env* env) {
     CUDA_TRY(env, cudaMalloc(&env->s_actions, c.N * c.n));
     CUDA_TRY(env, cudaMalloc(&env->s_rewards, c.N * c.n * 4));
     CUDA_TRY(env, cudaMalloc(&env->s_dones, c.N * c.n));
+    CUDA_TRY(env, cudaMalloc(&env->d_chunk_done, 128 * sizeof(unsigned)));
+    CUDA_TRY(env, cudaMemset(env->d_chunk_done, 0, 128 * sizeof(unsigned)));
     for (int i = 0; i < 2; ++i) {
         CUDA_TRY(env, cudaStreamCreateWithFlags(&env->pipe_stream[i], cudaStreamNonBlocking));
         CUDA_TRY(env, cudaEventCreateWithFlags(&env->pipe_end[i], cudaEventDisableTiming));
     }
     CUDA_TRY(env, cudaEventCreateWithFlags(&env->pipe_begin, cudaEventDisableTiming));
+    return DRL_OK;
+}
+
+// cuStreamWaitValue32 through the runtime's driver entry point lookup (no link-time dependency on libcuda)
+typedef CUresult (*stream_value32_fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+static stream_value32_fn driver_entry(const char* name) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    const bool ok = cudaGetDriverEntryPoint(name, &p, cudaEnableDefault, &qr) == cudaSuccess && qr == cudaDriverEntryPointSuccess;
+    (void)cudaGetLastError();
+    return ok ? (stream_value32_fn)p : nullptr;
+}
+static stream_value32_fn stream_wait_value32() {
+    static stream_value32_fn fn = driver_entry("cuStreamWaitValue32");
+    return fn;
+}
+static stream_value32_fn stream_write_value32() {
+    static stream_value32_fn fn = driver_entry("cuStreamWriteValue32");
+    return fn;
+}
+
+// drl_step_host, warp mode: ONE ticketed step launch over the whole slice.  The envs are stepped in index order
+// (tickets), every warp reports the envs it has finished to per-chunk counters, and the copy stream waits on those
+// counters (stream memory op) to move each chunk's rewards and dones to the host while later chunks are still being
+// stepped.  Compared with one launch per chunk this has no kernel boundaries: no start-up, tail and quantisation loss
+// per chunk (with tickets all workers of a launch finish together, so consecutive chunk launches no longer overlap).
+static int step_host_single(drl_env* env, const uint32_t key[2], const int8_t* h_actions, float* h_rewards, uint8_t* h_dones,
+                            void* d_obs, cudaStream_t s, stream_value32_fn wait32) {
+    const DevCfg& c = env->dc;
+    const long long n = c.n;
+    int shift = 15;                                           // chunks of 2^shift envs, at most 17 of them
+    while ((c.N >> shift) > 16) ++shift;
+    const long long per = 1ll << shift;
+    const int chunks = (int)((c.N + per - 1) >> shift);
+    cudaStream_t ps = env->pipe_stream[0], pin = env->pipe_stream[1];
+    stream_value32_fn write32 = stream_write_value32();
+    unsigned* const flags_in = env->d_chunk_done + 64;
+    const unsigned epoch = ++env->host_epoch;
+    int rc = drl_split_keys(env, key, env->s_keys, s);       // split(key, N), train_jax.py:53
+    if (rc) return rc;
+    CUDA_TRY(env, cudaMemsetAsync(env->d_chunk_done, 0, 64 * sizeof(unsigned), s));
+    if (write32 == nullptr) CUDA_TRY(env, cudaMemcpyAsync(env->s_actions, h_actions, c.N * n, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(env, cudaEventRecord(env->pipe_begin, s));     // the copy streams start behind the caller's earlier work
+    if (write32 != nullptr) {
+        // actions: chunk by chunk on the input stream, each copy followed by its flag; the step launch below starts at
+        // once and its warps wait (only at the very beginning, the copies are far ahead of the stepping) for the flag
+        // of the chunk they are about to read
+        CUDA_TRY(env, cudaStreamWaitEvent(pin, env->pipe_begin, 0));
+        for (int k = 0; k < chunks; ++k) {
+            const long long first = (long long)k << shift;
+            const long long count = c.N - first < per ? c.N - first : per;
+            CUDA_TRY(env, cudaMemcpyAsync(env->s_actions + first * n, h_actions + first * n, count * n, cudaMemcpyHostToDevice, pin));
+            if (write32((CUstream)pin, (CUdeviceptr)(uintptr_t)(flags_in + k), (cuuint32_t)epoch, CU_STREAM_WRITE_VALUE_DEFAULT) !=
+                CUDA_SUCCESS)
+                return fail(env, DRL_ECUDA, "drl_step_host: cuStreamWriteValue32 failed%s");
+        }
+    }
+    rc = launch_step(env, 0, c.N, env->s_keys, env->s_actions, env->s_rewards, env->s_dones, (float*)d_obs, s, 0, nullptr,
+                     nullptr, 100, env->d_chunk_done, shift, write32 != nullptr ? flags_in : nullptr, epoch);
+    if (rc) return rc;
+    CUDA_TRY(env, cudaStreamWaitEvent(ps, env->pipe_begin, 0));
+    for (int k = 0; k < chunks; ++k) {
+        const long long first = (long long)k << shift;
+        const long long count = c.N - first < per ? c.N - first : per;
+        if (wait32((CUstream)ps, (CUdeviceptr)(uintptr_t)(env->d_chunk_done + k), (cuuint32_t)count, CU_STREAM_WAIT_VALUE_GEQ) !=
+            CUDA_SUCCESS)
+            return fail(env, DRL_ECUDA, "drl_step_host: cuStreamWaitValue32 failed%s");
+        CUDA_TRY(env, cudaMemcpyAsync(h_rewards + first * n, env->s_rewards + first * n, count * n * 4, cudaMemcpyDeviceToHost, ps));
+        CUDA_TRY(env, cudaMemcpyAsync(h_dones + first * n, env->s_dones + first * n, count * n, cudaMemcpyDeviceToHost, ps));
+    }
+    CUDA_TRY(env, cudaEventRecord(env->pipe_end[0], ps));
+    CUDA_TRY(env, cudaStreamWaitEvent(s, env->pipe_end[0], 0));
+    CUDA_TRY(env, cudaStreamSynchronize(s));
     return DRL_OK;
 }
 
@@ -948,7 +1052,23 @@ int drl_step_host(drl_env* env, const uint32_t key[2], const int8_t* h_actions, 
     const DevCfg& c = env->dc;
     const long long n = c.n;
     cudaStream_t s = (cudaStream_t)stream;
-    const StepKeys sk = {key, nullptr, 0};                          // per-env keys are hashed inside the step kernel
+    {
+        const char* hp = getenv("DRL_HOST_PIPE");          // A/B switch: "chunks" = one step launch per chunk
+        const bool want_chunks = hp && hp[0] == 'c';
+        stream_value32_fn wait32 = stream_wait_value32();
+        if (pick_step_hostpipe(env) != nullptr && !env->static_order && !h_obs && !want_chunks && wait32 != nullptr)
+            return step_host_single(env, key, h_actions, h_rewards, h_dones, d_obs, s, wait32);
+    }
+    // split(key, N) (train_jax.py:53): one 11-us kernel into handle-owned scratch ahead of the pipeline.  (Hashing the
+    // keys inside the step kernels -- drl_step_keyed -- saves the 8 bytes per env but costs ~50 us per 1M envs there:
+    // the extra code pushes the step loop further out of the instruction cache; DRL_HOST_FUSE_KEYS=1 switches back.)
+    const char* fk = getenv("DRL_HOST_FUSE_KEYS");
+    const bool fuse_keys = fk && fk[0] == '1';
+    const StepKeys sk = {key, nullptr, 0};
+    if (!fuse_keys) {
+        rc = drl_split_keys(env, key, env->s_keys, stream);
+        if (rc) return rc;
+    }
     CUDA_TRY(env, cudaEventRecord(env->pipe_begin, s));
     // chunks of a whole number of 1024-env blocks: H2D actions -> step+obs -> D2H rewards, dones (, obs)
     const long long kMinChunk = 32768;
@@ -958,14 +1078,16 @@ int drl_step_host(drl_env* env, const uint32_t key[2], const int8_t* h_actions, 
     chunks = chunks < 1 ? 1 : chunks > max_chunks ? max_chunks : chunks;
     const long long per = ((c.N + chunks - 1) / chunks + 1023) / 1024 * 1024;
     const long long obs_env = (long long)c.obs_n * c.W2 * 6;     // floats per env
+    int grid_pct = 100;          // smaller grids (two chunk launches side by side) measured slower: 3.1e9 at 50 % vs 3.4e9
+    if (const char* gp = getenv("DRL_HOST_GRID_PCT")) grid_pct = atoi(gp) < 10 ? 10 : atoi(gp) > 100 ? 100 : atoi(gp);   // A/B switch
     int used = 0;
     for (long long first = 0; first < c.N; first += per, ++used) {
         const long long count = c.N - first < per ? c.N - first : per;
         cudaStream_t ps = env->pipe_stream[used & 1];
         if (used < 2) CUDA_TRY(env, cudaStreamWaitEvent(ps, env->pipe_begin, 0));
         CUDA_TRY(env, cudaMemcpyAsync(env->s_actions + first * n, h_actions + first * n, count * n, cudaMemcpyHostToDevice, ps));
-        rc = launch_step(env, first, count, nullptr, env->s_actions, env->s_rewards, env->s_dones, (float*)d_obs, ps, 1 + used,
-                         nullptr, &sk);
+        rc = launch_step(env, first, count, fuse_keys ? nullptr : env->s_keys, env->s_actions, env->s_rewards, env->s_dones,
+                         (float*)d_obs, ps, 1 + used, nullptr, fuse_keys ? &sk : nullptr, grid_pct);
         if (rc) return rc;
         CUDA_TRY(env, cudaMemcpyAsync(h_rewards + first * n, env->s_rewards + first * n, count * n * 4, cudaMemcpyDeviceToHost, ps));
         CUDA_TRY(env, cudaMemcpyAsync(h_dones + first * n, env->s_dones + first * n, count * n, cudaMemcpyDeviceToHost, ps));
@@ -985,8 +1107,11 @@ int drl_rollout_random(drl_env* env, uint32_t rng[2], int32_t steps, int32_t res
                        void* d_actions, void* d_rewards, void* d_dones, void* d_obs, void* stream) {
     if (!env || !rng || steps < 0 || !d_keys || !d_actions) return DRL_EINVAL;
     int launches = 0;
-    const char* nf = getenv("DRL_NO_FUSE");                 // A/B switch: separate randint / key-split kernels
-    const bool fused = !(nf && nf[0] == '1') && d_rewards && d_dones && env->d_ground &&
+    // A/B switch DRL_FUSE_KEYS=1: hash split(key, N) inside the step kernel instead of the 11-us split kernel.  Measured
+    // slower since the step kernels draw tickets (0.990 vs 0.957 ms per step at 1M envs): the step loop no longer fits the
+    // instruction cache (ncu: no_instruction is its top stall) and the hash adds to it.
+    const char* fz = getenv("DRL_FUSE_KEYS");
+    const bool fused = fz && fz[0] == '1' && d_rewards && d_dones && env->d_ground &&
                        env->cfg.num_envs_global * env->dc.n < (1ll << 32);
     const char* fa = getenv("DRL_FUSE_ACTIONS");
     const bool fuse_actions = fused && fa && fa[0] == '1';

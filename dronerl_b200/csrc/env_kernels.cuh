@@ -67,14 +67,24 @@ struct DevCfg {
     uint32_t ak[4];            // k1, k2 = split(action key) of _randint (train_jax.py:43-44)
     uint32_t act_span, act_mult;
     long long Ng, goff;        // global env count, global index of this launch's env 0
+    // drl_step_host's single-launch pipeline: after a group of envs is stepped (state, rewards, dones stored and
+    // fenced) the warp adds its env count to chunk_done[env >> chunk_shift]; the copy stream waits on those counters
+    // (cuStreamWaitValue32) and moves each chunk's rewards / dones to the host while later chunks are still stepped
+    unsigned* chunk_done;      // nullptr: off
+    int chunk_shift;
+    // ... and its input side: the actions arrive chunk by chunk from the host while the launch is already running;
+    // chunk_in[env >> chunk_shift] is set to in_epoch (stream memory op behind each copy) once a chunk has landed
+    const unsigned* chunk_in;  // nullptr: off
+    unsigned in_epoch;
 };
 
 // keys[e] word w of jax.random.split(parent, Ng)[goff + e]  (train_jax.py:53)
-__device__ __forceinline__ uint32_t derive_key_word(const DevCfg& c, long long e, int w) {
+// (Not inlined: both derivations are off the default path, and the step loops are instruction-cache bound.)
+__device__ __noinline__ uint32_t derive_key_word(const DevCfg& c, long long e, int w) {
     return drl_random_bits_at(c.pk0, c.pk1, (uint64_t)(2 * c.Ng), (uint64_t)(2 * (c.goff + e) + w));
 }
 // int(jax.random.randint(key, (Ng, n), 0, span))[goff + e, j]: _randint's two-draw reduction (train_jax.py:44)
-__device__ __forceinline__ int derive_action(const DevCfg& c, long long e, int j) {
+__device__ __noinline__ int derive_action(const DevCfg& c, long long e, int j) {
     const uint64_t total = (uint64_t)(c.Ng * c.n), a = (uint64_t)((c.goff + e) * c.n + j);
     const uint32_t hi = drl_random_bits_at(c.ak[0], c.ak[1], total, a);
     const uint32_t lo = drl_random_bits_at(c.ak[2], c.ak[3], total, a);

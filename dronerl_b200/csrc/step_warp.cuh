@@ -9,6 +9,10 @@
 #pragma once
 #include "env_kernels.cuh"
 
+#ifndef DRL_KEYVAR
+#define DRL_KEYVAR 0
+#endif
+
 namespace drl {
 
 template <int NV>
@@ -25,7 +29,9 @@ __device__ __forceinline__ int zero_bytes16(const uint4& v) {
     return 16 - (nz(v.x) + nz(v.y) + nz(v.z) + nz(v.w));
 }
 
-template <int NB, int Q, class D>
+// HP: instance for drl_step_host's single-launch pipeline (input flags / completion counters compiled in only there:
+// the step loop is instruction-cache bound and every extra line in it costs time).
+template <int NB, int Q, class D, bool HP = false>
 __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsigned char* base, uint8_t* __restrict__ ground,
                                                uint32_t* __restrict__ drones, const uint32_t* __restrict__ keys,
                                                const int8_t* __restrict__ actions, float* __restrict__ rewards,
@@ -64,6 +70,18 @@ __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsi
         const long long e0 = g * Q;
         if (e0 < c.N) {
             const int nq = (int)min((long long)Q, c.N - e0);
+            if (HP && c.chunk_in != nullptr) {              // host pipeline: wait until this group's actions have landed
+                if (lane == 0) {
+                    const unsigned* f = c.chunk_in + (e0 >> c.chunk_shift);
+                    unsigned v;
+                    for (;;) {
+                        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+                        if ((int)(v - c.in_epoch) >= 0) break;
+                        __nanosleep(100);
+                    }
+                }
+                __syncwarp();
+            }
 #pragma unroll
             for (int v = 0; v < NV; ++v)
                 if (lane + 32 * v < nvec * nq) nxt.gv[v] = reinterpret_cast<const uint4*>(ground + e0 * GS)[lane + 32 * v];
@@ -78,12 +96,28 @@ __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsi
                     nxt.k1 = kk.y;
                 }
             }
+#if DRL_KEYVAR != 2
             if (c.key_mode) {       // lanes 0 and 1 of each env hash one key word each (S >= 2)
+#if DRL_KEYVAR == 1
+                const uint32_t w = c.pk0 + (uint32_t)(e0 + sub) * 2u + (li & 1);
+#else
                 const uint32_t w = derive_key_word(c, min(e0 + sub, c.N - 1), li & 1);
+#endif
                 nxt.k0 = __shfl_sync(FULL, w, sub * S);
                 nxt.k1 = __shfl_sync(FULL, w, sub * S + (S > 1 ? 1 : 0));
             }
+#endif
         }
+    };
+    auto late_keys = [&](long long g) {
+#if DRL_KEYVAR == 2
+        const long long e0 = g * Q;
+        if (c.key_mode && e0 < c.N) {
+            const uint32_t w = derive_key_word(c, min(e0 + sub, c.N - 1), li & 1);
+            nxt.k0 = __shfl_sync(FULL, w, sub * S);
+            nxt.k1 = __shfl_sync(FULL, w, sub * S + (S > 1 ? 1 : 0));
+        }
+#endif
     };
     // Group order.  A static grid-stride order lets the warps drift apart, so the addresses being written at any
     // moment spread over a wide range and the obs stream loses DRAM locality: measured 6.3 TB/s for the bare tile
@@ -345,6 +379,12 @@ __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsi
             }
         }
         env_steps += nq;
+        late_keys(gn);
+        if (HP && c.chunk_done != nullptr) {                // the group's results are complete: tell the copy stream
+            __threadfence();
+            __syncwarp();
+            if (lane == 0) atomicAdd(c.chunk_done + (e0 >> c.chunk_shift), (unsigned)nq);
+        }
     }
     tile_drain(lane);
     if (queue != nullptr && lane == 0) {

@@ -118,9 +118,12 @@ def test_sharded_slices_equal_unsharded(c_oracle):
     np.testing.assert_array_equal(got_d, full.drones_raw.cpu().numpy())
 
 
-@pytest.mark.parametrize('N,G,n', [(70001, 9, 4), (300000, 8, 3), (999, 9, 4)])
-def test_step_host_pipeline_equals_device_step(N, G, n):
-    """drl_step_host (host buffers, chunked over two side streams) == drl_step on the same state/keys/actions."""
+@pytest.mark.parametrize('N,G,n,copy_obs', [(70001, 9, 4, True), (70001, 9, 4, False), (300000, 8, 3, False),
+                                            (999, 9, 4, True), (999, 9, 4, False), (1100003, 9, 4, False)])
+def test_step_host_pipeline_equals_device_step(N, G, n, copy_obs):
+    """drl_step_host (host buffers) == drl_step on the same state/keys/actions: the single-launch pipeline (rewards /
+    dones copied out chunk by chunk behind per-chunk completion counters while later envs are still stepped) and,
+    when the observations are copied out too, one launch per chunk over two side streams."""
     import ctypes
     import dronerl_b200 as drl
     from dronerl_b200 import _lib
@@ -139,7 +142,7 @@ def test_step_host_pipeline_equals_device_step(N, G, n):
         h_rew = torch.empty((N, n), dtype=torch.float32).pin_memory()
         h_done = torch.empty((N, n), dtype=torch.uint8).pin_memory()
         d_obs = torch.empty((N, n, W, W, 6), dtype=torch.float32, device='cuda')
-        h_obs = torch.empty((N, n, W, W, 6), dtype=torch.float32).pin_memory() if N < 100000 else None
+        h_obs = torch.empty((N, n, W, W, 6), dtype=torch.float32).pin_memory() if copy_obs else None
         h.check(h.lib.drl_step_host(h.ptr, _lib.key_array(key), ctypes.c_void_p(h_act.data_ptr()),
                                     ctypes.c_void_p(h_rew.data_ptr()), ctypes.c_void_p(h_done.data_ptr()), _vp(d_obs),
                                     ctypes.c_void_p(h_obs.data_ptr() if h_obs is not None else 0), _stream()))
