@@ -604,7 +604,7 @@ static void fill_derivation(const drl_env* env, DevCfg& dc, long long first, con
 static int launch_step(drl_env* env, long long first, long long count, const uint32_t* d_keys, const int8_t* d_actions,
                        float* d_rewards, uint8_t* d_dones, float* d_obs, cudaStream_t s, int slot, int* launches,
                        const StepKeys* sk = nullptr, int grid_pct = 100, unsigned* chunk_done = nullptr, int chunk_shift = 0,
-                       const unsigned* chunk_in = nullptr, unsigned in_epoch = 0) {
+                       const unsigned* chunk_in = nullptr, unsigned in_epoch = 0, int in_shift = 0) {
     // grid_pct < 100: launch on that share of the resident CTA count, so that chunk launches on two streams run side
     // by side (with ticketed env order every worker of a launch finishes at the same moment; a full-size grid would
     // leave the next chunk's start-up and this chunk's tail exposed at every boundary)
@@ -614,6 +614,7 @@ static int launch_step(drl_env* env, long long first, long long count, const uin
     dc.chunk_shift = chunk_shift;
     dc.chunk_in = chunk_in;
     dc.in_epoch = in_epoch;
+    dc.in_shift = in_shift;
     fill_derivation(env, dc, first, sk);
     const long long n = dc.n;
     uint8_t* ground = env->d_ground + first * dc.GS;
@@ -994,10 +995,11 @@ static int step_host_single(drl_env* env, const uint32_t key[2], const int8_t* h
                             void* d_obs, cudaStream_t s, stream_value32_fn wait32) {
     const DevCfg& c = env->dc;
     const long long n = c.n;
-    int shift = 15;                                           // chunks of 2^shift envs, at most 17 of them
+    int shift = 15;                                           // output chunks of 2^shift envs, at most 17 of them
     while ((c.N >> shift) > 16) ++shift;
-    const long long per = 1ll << shift;
-    const int chunks = (int)((c.N + per - 1) >> shift);
+    const int in_shift = shift + 1;                           // input chunks: twice as large
+    const long long per = 1ll << shift, per_in = 1ll << in_shift;
+    const int chunks = (int)((c.N + per - 1) >> shift), chunks_in = (int)((c.N + per_in - 1) >> in_shift);
     cudaStream_t ps = env->pipe_stream[0], pin = env->pipe_stream[1];
     stream_value32_fn write32 = stream_write_value32();
     unsigned* const flags_in = env->d_chunk_done + 64;
@@ -1007,23 +1009,31 @@ static int step_host_single(drl_env* env, const uint32_t key[2], const int8_t* h
     CUDA_TRY(env, cudaMemsetAsync(env->d_chunk_done, 0, 64 * sizeof(unsigned), s));
     if (write32 == nullptr) CUDA_TRY(env, cudaMemcpyAsync(env->s_actions, h_actions, c.N * n, cudaMemcpyHostToDevice, s));
     CUDA_TRY(env, cudaEventRecord(env->pipe_begin, s));     // the copy streams start behind the caller's earlier work
+    // The step launch goes first: its warps wait (only at the very beginning -- the copies run far ahead of the
+    // stepping) for the flag of the input chunk they are about to read, so the GPU is already stepping chunk 0 while
+    // the host is still enqueueing the other copies.
+    rc = launch_step(env, 0, c.N, env->s_keys, env->s_actions, env->s_rewards, env->s_dones, (float*)d_obs, s, 0, nullptr,
+                     nullptr, 100, env->d_chunk_done, shift, write32 != nullptr ? flags_in : nullptr, epoch, in_shift);
+    if (rc) return rc;
+    // From here on a failed enqueue must not leave the launch waiting for flags that will never be written.
+    auto bail = [&](const char* what) {
+        if (write32 != nullptr)
+            for (int k = 0; k < chunks_in; ++k) (void)write32((CUstream)pin, (CUdeviceptr)(uintptr_t)(flags_in + k), epoch, 0u);
+        (void)cudaGetLastError();
+        return fail(env, DRL_ECUDA, "drl_step_host: %s failed", what);
+    };
     if (write32 != nullptr) {
-        // actions: chunk by chunk on the input stream, each copy followed by its flag; the step launch below starts at
-        // once and its warps wait (only at the very beginning, the copies are far ahead of the stepping) for the flag
-        // of the chunk they are about to read
-        CUDA_TRY(env, cudaStreamWaitEvent(pin, env->pipe_begin, 0));
-        for (int k = 0; k < chunks; ++k) {
-            const long long first = (long long)k << shift;
-            const long long count = c.N - first < per ? c.N - first : per;
-            CUDA_TRY(env, cudaMemcpyAsync(env->s_actions + first * n, h_actions + first * n, count * n, cudaMemcpyHostToDevice, pin));
+        if (cudaStreamWaitEvent(pin, env->pipe_begin, 0) != cudaSuccess) return bail("cudaStreamWaitEvent");
+        for (int k = 0; k < chunks_in; ++k) {
+            const long long first = (long long)k << in_shift;
+            const long long count = c.N - first < per_in ? c.N - first : per_in;
+            if (cudaMemcpyAsync(env->s_actions + first * n, h_actions + first * n, count * n, cudaMemcpyHostToDevice, pin) != cudaSuccess)
+                return bail("cudaMemcpyAsync of the actions");
             if (write32((CUstream)pin, (CUdeviceptr)(uintptr_t)(flags_in + k), (cuuint32_t)epoch, CU_STREAM_WRITE_VALUE_DEFAULT) !=
                 CUDA_SUCCESS)
-                return fail(env, DRL_ECUDA, "drl_step_host: cuStreamWriteValue32 failed%s");
+                return bail("cuStreamWriteValue32");
         }
     }
-    rc = launch_step(env, 0, c.N, env->s_keys, env->s_actions, env->s_rewards, env->s_dones, (float*)d_obs, s, 0, nullptr,
-                     nullptr, 100, env->d_chunk_done, shift, write32 != nullptr ? flags_in : nullptr, epoch);
-    if (rc) return rc;
     CUDA_TRY(env, cudaStreamWaitEvent(ps, env->pipe_begin, 0));
     for (int k = 0; k < chunks; ++k) {
         const long long first = (long long)k << shift;

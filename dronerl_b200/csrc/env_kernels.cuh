@@ -73,9 +73,10 @@ struct DevCfg {
     unsigned* chunk_done;      // nullptr: off
     int chunk_shift;
     // ... and its input side: the actions arrive chunk by chunk from the host while the launch is already running;
-    // chunk_in[env >> chunk_shift] is set to in_epoch (stream memory op behind each copy) once a chunk has landed
+    // chunk_in[env >> in_shift] is set to in_epoch (stream memory op behind each copy) once a chunk has landed
     const unsigned* chunk_in;  // nullptr: off
     unsigned in_epoch;
+    int in_shift;
 };
 
 // keys[e] word w of jax.random.split(parent, Ng)[goff + e]  (train_jax.py:53)

@@ -9,10 +9,6 @@
 #pragma once
 #include "env_kernels.cuh"
 
-#ifndef DRL_KEYVAR
-#define DRL_KEYVAR 0
-#endif
-
 namespace drl {
 
 template <int NV>
@@ -66,13 +62,15 @@ __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsi
     int tsel = 0;
 
     GroupInputs<NV> nxt = {};
+    int in_ready = -1;                            // HP: input chunk whose flag this warp has already seen
     auto prefetch = [&](long long g) {
         const long long e0 = g * Q;
         if (e0 < c.N) {
             const int nq = (int)min((long long)Q, c.N - e0);
-            if (HP && c.chunk_in != nullptr) {              // host pipeline: wait until this group's actions have landed
+            if (HP && c.chunk_in != nullptr && (int)(e0 >> c.in_shift) != in_ready) {   // host pipeline: wait until this
+                in_ready = (int)(e0 >> c.in_shift);                                        // group's input chunk has landed
                 if (lane == 0) {
-                    const unsigned* f = c.chunk_in + (e0 >> c.chunk_shift);
+                    const unsigned* f = c.chunk_in + in_ready;
                     unsigned v;
                     for (;;) {
                         asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
@@ -96,28 +94,12 @@ __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsi
                     nxt.k1 = kk.y;
                 }
             }
-#if DRL_KEYVAR != 2
             if (c.key_mode) {       // lanes 0 and 1 of each env hash one key word each (S >= 2)
-#if DRL_KEYVAR == 1
-                const uint32_t w = c.pk0 + (uint32_t)(e0 + sub) * 2u + (li & 1);
-#else
                 const uint32_t w = derive_key_word(c, min(e0 + sub, c.N - 1), li & 1);
-#endif
                 nxt.k0 = __shfl_sync(FULL, w, sub * S);
                 nxt.k1 = __shfl_sync(FULL, w, sub * S + (S > 1 ? 1 : 0));
             }
-#endif
         }
-    };
-    auto late_keys = [&](long long g) {
-#if DRL_KEYVAR == 2
-        const long long e0 = g * Q;
-        if (c.key_mode && e0 < c.N) {
-            const uint32_t w = derive_key_word(c, min(e0 + sub, c.N - 1), li & 1);
-            nxt.k0 = __shfl_sync(FULL, w, sub * S);
-            nxt.k1 = __shfl_sync(FULL, w, sub * S + (S > 1 ? 1 : 0));
-        }
-#endif
     };
     // Group order.  A static grid-stride order lets the warps drift apart, so the addresses being written at any
     // moment spread over a wide range and the obs stream loses DRAM locality: measured 6.3 TB/s for the bare tile
@@ -132,6 +114,20 @@ __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsi
         unsigned t = 0;
         if (lane == 0) t = atomicAdd(queue, 1u);
         return total_warps + (long long)__shfl_sync(FULL, t, 0);
+    };
+    // Host pipeline (HP): a finished group is reported to the copy stream one group later, right before the next
+    // write-back -- by then its stores (and its tile stores) have long completed, so the fence that orders them before
+    // the counter update has nothing to wait for (reporting at the end of the group's own iteration cost 1.1 us per
+    // group: 0.968 vs 0.926 ms per 1M envs).
+    int sig_chunk = -1;
+    int sig_n = 0;
+    auto report = [&]() {
+        if (HP && c.chunk_done != nullptr && sig_chunk >= 0) {
+            __threadfence();
+            __syncwarp();
+            if (lane == 0) atomicAdd(c.chunk_done + sig_chunk, (unsigned)sig_n);
+            sig_chunk = -1;
+        }
     };
     long long g = first_group;
     prefetch(g);
@@ -354,6 +350,7 @@ __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsi
         __syncwarp();
 
         // ---- write back, observations -----------------------------------------------------------------
+        report();
         const uint32_t rec = (uint32_t)rx | ((uint32_t)ry << 8) | ((uint32_t)carry << 16) | ((uint32_t)ch << 24);
 #pragma unroll
         for (int v = 0; v < NV; ++v)
@@ -379,14 +376,10 @@ __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsi
             }
         }
         env_steps += nq;
-        late_keys(gn);
-        if (HP && c.chunk_done != nullptr) {                // the group's results are complete: tell the copy stream
-            __threadfence();
-            __syncwarp();
-            if (lane == 0) atomicAdd(c.chunk_done + (e0 >> c.chunk_shift), (unsigned)nq);
-        }
+        if (HP) { sig_chunk = (int)(e0 >> c.chunk_shift); sig_n = nq; }   // reported at the next group's write-back
     }
     tile_drain(lane);
+    report();
     if (queue != nullptr && lane == 0) {
         __threadfence();                                    // the last ticket drawn is ordered before the exit count
         if (atomicAdd(queue + 1, 1u) == (unsigned)(total_warps - 1)) {
