@@ -163,7 +163,10 @@ int drl_get_obs(drl_env* env, void* d_obs, void* stream);
  * returns after the results have landed (stream synchronised).  ``key`` is the
  * parent key the per-env keys are split from (train_jax.py:52-53).  Observations
  * stay on the device in ``d_obs`` (the reference keeps them there for the agent,
- * train_jax.py:55-56); pass ``h_obs`` non-NULL to also copy them out. */
+ * train_jax.py:55-56); pass ``h_obs`` non-NULL to also copy them out.
+ * The host buffers should be page-locked: the copies are asynchronous and overlap
+ * the step (actions arrive and rewards / dones leave chunk by chunk while one
+ * launch steps the slice in env order; pageable memory works but serialises). */
 int drl_step_host(drl_env* env, const uint32_t key[2], const int8_t* h_actions, float* h_rewards,
                   uint8_t* h_dones, void* d_obs, float* h_obs, void* stream);
 
