@@ -287,61 +287,54 @@ __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsi
                     if (((validm >> s) & 1u) && sgq[slot_cell<32>(lane, s, d.H())] == 0) { freem |= 1u << s; ++fc; }
                 return fc;
             };
-            // The three spawns of a step run as three passes of ONE loop body, so the noise generation and the rank
-            // extraction exist once in the code: the step loop is instruction-cache bound (ncu: no_instruction is
-            // its top stall), three inlined copies of both cost more than the few uniform branches here.
             uint32_t mant[2 * NB];
-            bool have_noise = false;                                // mant holds the noise of spawn_key (qs0, qs1)
-#pragma unroll 1
-            for (int ph = 0; ph < 3; ++ph) {
-                uint32_t nk0 = qs0, nk1 = qs1, fillm = 0, maskm = 0;
-                int J = 0;
-                if (ph == 0) {
-                    // S8 packet respawn (env.py:197-203)
-                    if (!(qP != 0 || qF1 < k)) continue;
-                    __syncwarp();                                   // pickup clears are visible
-                    if (qF1 < k) capture_oldsky();
-                    scan_free();
-                    maskm = freem;
-                    J = qF1 < k ? k : 32 - __clz(qP);
-                    fillm = qP;
-                } else if (ph == 1) {
-                    // S9 dropzone respawn (env.py:205-212): same spawn_key, hence the same noise
-                    if (!(qD != 0 || qF1 - __popc(qP) < k)) continue;
-                    __syncwarp();                                   // mask zeroing follows the packet spawn's writes
-                    if (mine && del_clear) sgq[tcell] = 0;
-                    __syncwarp();
-                    const int F2 = (int)__reduce_add_sync(FULL, (unsigned)scan_free());
-                    if (!(qD != 0 || F2 < k)) continue;
+            bool have_noise = false;
+            auto ensure_noise = [&]() {
+                if (!have_noise) { noise_mantissas<32, NB>(lane, d, qs0, qs1, mant); have_noise = true; }
+            };
+
+            // S8 packet respawn (env.py:197-203)
+            if (qP != 0 || qF1 < k) {
+                __syncwarp();                                       // pickup clears are visible
+                if (qF1 < k) capture_oldsky();
+                scan_free();
+                ensure_noise();
+                const int J = qF1 < k ? k : 32 - __clz(qP);
+                extract_ranks<32, NB>(grp, lane, d, mant, freem, validm, J, [&](int j, int pos) {
+                    if (lane == 0) sgq[pos] = (j < n && ((qP >> j) & 1u)) ? PACKET : 0;
+                });
+            }
+            // S9 dropzone respawn (env.py:205-212): same spawn_key, hence the same noise
+            if (qD != 0 || qF1 - __popc(qP) < k) {
+                __syncwarp();                                       // mask zeroing follows the packet spawn's writes
+                if (mine && del_clear) sgq[tcell] = 0;
+                __syncwarp();
+                const int F2 = (int)__reduce_add_sync(FULL, (unsigned)scan_free());
+                if (qD != 0 || F2 < k) {
                     if (F2 < k) capture_oldsky();
-                    maskm = freem;
-                    J = F2 < k ? k : 32 - __clz(qD);
-                    fillm = qD;
-                } else {
-                    // S11 respawn (env.py:222-230) and S12 pickup on respawn (env.py:233-241)
-                    if (qDone == 0) continue;
-                    nk0 = __shfl_sync(FULL, rk0, ql);
-                    nk1 = __shfl_sync(FULL, rk1, ql);
-                    // p_choice[x, y] = False for survivors (row = x), [-1, -1] -> last cell; &= ~(old ground == SKY)
-                    if (mine && surv) codeq[x * G + y] = 1;
-                    __syncwarp();                                   // also orders the ground writes above
-                    capture_oldsky();
+                    ensure_noise();
+                    const int J = F2 < k ? k : 32 - __clz(qD);
+                    extract_ranks<32, NB>(grp, lane, d, mant, freem, validm, J, [&](int j, int pos) {
+                        if (lane == 0) sgq[pos] = (j < n && ((qD >> j) & 1u)) ? DROPZONE : 0;
+                    });
+                }
+            }
+            // S11 respawn (env.py:222-230) and S12 pickup on respawn (env.py:233-241)
+            if (qDone != 0) {
+                const uint32_t qr0 = __shfl_sync(FULL, rk0, ql), qr1 = __shfl_sync(FULL, rk1, ql);
+                // p_choice[x, y] = False for survivors (row = x), [-1, -1] -> last cell; &= ~(old ground == SKY)
+                if (mine && surv) codeq[x * G + y] = 1;
+                __syncwarp();                                       // also orders the ground writes above
+                capture_oldsky();
+                uint32_t candm = 0;
 #pragma unroll
-                    for (int s = 0; s < 2 * NB; ++s) {
-                        const int cl = slot_cell<32>(lane, s, d.H());
-                        if (((validm >> s) & 1u) && !((oldsky >> s) & 1u) && cl != G2 - 1 && codeq[cl] == 0) maskm |= 1u << s;
-                    }
-                    J = 32 - __clz(qDone);
-                    have_noise = false;                             // the second split's key: new noise
+                for (int s = 0; s < 2 * NB; ++s) {
+                    const int cl = slot_cell<32>(lane, s, d.H());
+                    if (((validm >> s) & 1u) && !((oldsky >> s) & 1u) && cl != G2 - 1 && codeq[cl] == 0) candm |= 1u << s;
                 }
-                if (!have_noise) {
-                    noise_mantissas<32, NB>(lane, d, nk0, nk1, mant);
-                    have_noise = ph < 2;
-                }
-                extract_ranks<32, NB>(grp, lane, d, mant, maskm, validm, J, [&](int j, int pos) {
-                    if (ph < 2) {
-                        if (lane == 0) sgq[pos] = (j < n && ((fillm >> j) & 1u)) ? (ph == 0 ? PACKET : DROPZONE) : 0;
-                    } else if (lane == ql + j && done) {
+                noise_mantissas<32, NB>(lane, d, qr0, qr1, mant);
+                extract_ranks<32, NB>(grp, lane, d, mant, candm, validm, 32 - __clz(qDone), [&](int j, int pos) {
+                    if (lane == ql + j && done) {
                         rx = (int)d.divG((uint32_t)pos);             // rank i -> drone i: x = pos // G, y = pos % G
                         ry = pos - rx * G;
                         if (sgq[pos] == PACKET) {                    // package_mask[new_x, new_y]: flat x*G+y == pos
@@ -351,7 +344,7 @@ __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsi
                         }
                     }
                 });
-                if (ph == 2 && mine && surv) codeq[x * G + y] = 0;   // restore the all-zero invariant
+                if (mine && surv) codeq[x * G + y] = 0;              // restore the all-zero invariant
             }
         }
         __syncwarp();
