@@ -339,27 +339,50 @@ k_obs_cta(const __grid_constant__ DevCfg c, const uint8_t* __restrict__ ground, 
 
 // ---- key / action derivation --------------------------------------------------------------------
 
-// keys_out[e] = split(key, Ng)[off + e]: flat words 2(off+e), 2(off+e)+1 of random_bits(key, 2 Ng)
-// (the parent key comes by value, or from device memory when ``dkey`` is set: CUDA-graph friendly)
+// jax.random.bits(key, (size,)) in the original counter layout is made of threefry blocks whose two output words are
+// elements b and half + b (half = ceil(size / 2)).  The derivation kernels below walk BLOCKS, not elements: one hash
+// serves two elements whenever both lie in the local range [first, first + count) -- always on one GPU, where the
+// range is the whole vector -- instead of hashing every block twice and dropping a word each time.
+// Blocks [bmin, bmin + nb) cover every element of the local range (host side: bits_block_range).
+struct BitsBlock { uint32_t c1; long long f0, f1; bool in0, in1; };
+__device__ __forceinline__ BitsBlock bits_block(long long b, long long size, long long first, long long count) {
+    const long long half = (size + 1) >> 1;
+    BitsBlock r;
+    r.f0 = b;
+    r.f1 = half + b;
+    r.c1 = r.f1 < size ? (uint32_t)r.f1 : 0u;              // odd sizes: the pad counter is zero
+    r.in0 = r.f0 >= first && r.f0 < first + count;
+    r.in1 = r.f1 < size && r.f1 >= first && r.f1 < first + count;
+    return r;
+}
+
+// out[i - 2 off] = flat word i of jax.random.split(key, Ng) for the local rows [off, off + Nl)  (train_jax.py:53);
+// the parent key comes by value, or from device memory when ``dkey`` is set (CUDA-graph friendly)
 __global__ void k_split_keys(uint32_t k0, uint32_t k1, const uint32_t* __restrict__ dkey, long long Ng, long long off,
-                             long long Nl, uint32_t* __restrict__ out) {
-    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;   // local flat word
-    if (i >= 2 * Nl) return;
+                             long long Nl, uint32_t* __restrict__ out, long long bmin, long long nb) {
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nb) return;
     if (dkey != nullptr) { k0 = dkey[0]; k1 = dkey[1]; }
-    out[i] = drl_random_bits_at(k0, k1, (uint64_t)(2 * Ng), (uint64_t)(2 * off + i));
+    const BitsBlock bb = bits_block(bmin + t, 2 * Ng, 2 * off, 2 * Nl);
+    uint32_t o0, o1;
+    drl_threefry2x32(k0, k1, (uint32_t)bb.f0, bb.c1, o0, o1);
+    if (bb.in0) out[bb.f0 - 2 * off] = o0;
+    if (bb.in1) out[bb.f1 - 2 * off] = o1;
 }
 
 // actions_out = int8(randint(key, (Ng, n), 0, maxval))[off : off + Nl]; (a0,a1),(b0,b1) = split(key)
 __global__ void k_randint(uint32_t a0, uint32_t a1, uint32_t b0, uint32_t b1, const uint32_t* __restrict__ dkeys,
                           long long total, long long first, long long count, uint32_t span, uint32_t mult,
-                          int8_t* __restrict__ out) {
-    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= count) return;
+                          int8_t* __restrict__ out, long long bmin, long long nb) {
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nb) return;
     if (dkeys != nullptr) { a0 = dkeys[0]; a1 = dkeys[1]; b0 = dkeys[2]; b1 = dkeys[3]; }
-    const uint32_t hi = drl_random_bits_at(a0, a1, (uint64_t)total, (uint64_t)(first + i));
-    const uint32_t lo = drl_random_bits_at(b0, b1, (uint64_t)total, (uint64_t)(first + i));
-    const uint32_t v = ((hi % span) * mult + (lo % span)) % span;
-    out[i] = (int8_t)v;
+    const BitsBlock bb = bits_block(bmin + t, total, first, count);
+    uint32_t hi0, hi1, lo0, lo1;                            // _randint's two draws, same counters under k1 and k2
+    drl_threefry2x32(a0, a1, (uint32_t)bb.f0, bb.c1, hi0, hi1);
+    drl_threefry2x32(b0, b1, (uint32_t)bb.f0, bb.c1, lo0, lo1);
+    if (bb.in0) out[bb.f0 - first] = (int8_t)(((hi0 % span) * mult + (lo0 % span)) % span);
+    if (bb.in1) out[bb.f1 - first] = (int8_t)(((hi1 % span) * mult + (lo1 % span)) % span);
 }
 
 // out[i] = split(key, num)[i] with the key read from device memory; one block, in-place safe (``out`` may
@@ -837,11 +860,29 @@ int drl_bind_state(drl_env* env, void* d_ground, void* d_drones) {
     return DRL_OK;
 }
 
+// Blocks of random_bits(size) that hold the elements [first, first + count): word-0 elements are their own block
+// index, word-1 elements sit half further.  One contiguous block range covering both (equal to [0, half) on one GPU;
+// a slice inside one half costs exactly its own blocks; only a slice straddling the middle covers extra blocks).
+static void bits_block_range(long long size, long long first, long long count, long long* bmin, long long* nb) {
+    const long long half = (size + 1) >> 1, end = first + count;
+    long long lo = half, hi = 0;
+    if (first < half) { lo = first; hi = end < half ? end : half; }
+    if (end > half) {
+        const long long l2 = (first > half ? first : half) - half, h2 = end - half;
+        lo = l2 < lo ? l2 : lo;
+        hi = h2 > hi ? h2 : hi;
+    }
+    *bmin = lo;
+    *nb = hi > lo ? hi - lo : 0;
+}
+
 int drl_split_n(const uint32_t key[2], int64_t num, int64_t offset, int64_t count, void* d_out, void* stream) {
     if (!key || !d_out || num < 1 || offset < 0 || count < 0 || offset + count > num || num > (1ll << 30)) return DRL_EINVAL;
     if (count == 0) return DRL_OK;
-    return launch(nullptr, "split kernel", (const void*)k_split_keys, (int)((2 * count + 255) / 256), 256, 0, stream, key[0],
-                  key[1], (const uint32_t*)nullptr, (long long)num, (long long)offset, (long long)count, (uint32_t*)d_out);
+    long long bmin, nb;
+    bits_block_range(2 * num, 2 * offset, 2 * count, &bmin, &nb);
+    return launch(nullptr, "split kernel", (const void*)k_split_keys, (int)((nb + 255) / 256), 256, 0, stream, key[0],
+                  key[1], (const uint32_t*)nullptr, (long long)num, (long long)offset, (long long)count, (uint32_t*)d_out, bmin, nb);
 }
 
 int drl_randint_n(const uint32_t key[2], int64_t total, int64_t first, int64_t count, int32_t maxval, void* d_out,
@@ -855,9 +896,11 @@ int drl_randint_n(const uint32_t key[2], int64_t total, int64_t first, int64_t c
     const uint32_t span = (uint32_t)maxval;
     uint32_t mult = 65536u % span;
     mult = (mult * mult) % span;
-    return launch(nullptr, "randint kernel", (const void*)k_randint, (int)((count + 255) / 256), 256, 0, stream, k1[0], k1[1],
+    long long bmin, nb;
+    bits_block_range(total, first, count, &bmin, &nb);
+    return launch(nullptr, "randint kernel", (const void*)k_randint, (int)((nb + 255) / 256), 256, 0, stream, k1[0], k1[1],
                   k2[0], k2[1], (const uint32_t*)nullptr, (long long)total, (long long)first, (long long)count, span, mult,
-                  (int8_t*)d_out);
+                  (int8_t*)d_out, bmin, nb);
 }
 
 int drl_key_split_dev(const void* d_key, int32_t num, void* d_out, void* stream) {
@@ -869,9 +912,11 @@ int drl_key_split_dev(const void* d_key, int32_t num, void* d_out, void* stream)
 int drl_split_keys_dev(drl_env* env, const void* d_key, void* d_keys_out, void* stream) {
     if (!env || !d_key || !d_keys_out) return DRL_EINVAL;
     CUDA_TRY(env, cudaSetDevice(env->cfg.device));
-    return launch(env, "split kernel", (const void*)k_split_keys, (int)((2 * env->dc.N + 255) / 256), 256, 0, stream, 0u, 0u,
+    long long bmin, nb;
+    bits_block_range(2 * env->cfg.num_envs_global, 2 * env->cfg.env_offset, 2 * env->dc.N, &bmin, &nb);
+    return launch(env, "split kernel", (const void*)k_split_keys, (int)((nb + 255) / 256), 256, 0, stream, 0u, 0u,
                   (const uint32_t*)d_key, (long long)env->cfg.num_envs_global, (long long)env->cfg.env_offset,
-                  (long long)env->dc.N, (uint32_t*)d_keys_out);
+                  (long long)env->dc.N, (uint32_t*)d_keys_out, bmin, nb);
 }
 
 int drl_randint_actions_dev(drl_env* env, const void* d_key, int32_t maxval, void* d_actions_out, void* stream) {
@@ -886,9 +931,11 @@ int drl_randint_actions_dev(drl_env* env, const void* d_key, int32_t maxval, voi
     const uint32_t span = (uint32_t)maxval;
     uint32_t mult = 65536u % span;
     mult = (mult * mult) % span;
-    return launch(env, "randint kernel", (const void*)k_randint, (int)((env->dc.N * n + 255) / 256), 256, 0, stream, 0u, 0u, 0u, 0u,
+    long long bmin, nb;
+    bits_block_range(total, env->cfg.env_offset * n, env->dc.N * n, &bmin, &nb);
+    return launch(env, "randint kernel", (const void*)k_randint, (int)((nb + 255) / 256), 256, 0, stream, 0u, 0u, 0u, 0u,
                   (const uint32_t*)k12, total, (long long)(env->cfg.env_offset * n), (long long)(env->dc.N * n), span, mult,
-                  (int8_t*)d_actions_out);
+                  (int8_t*)d_actions_out, bmin, nb);
 }
 
 int drl_split_keys(drl_env* env, const uint32_t key[2], void* d_keys_out, void* stream) {

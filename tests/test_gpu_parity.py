@@ -154,6 +154,67 @@ def test_step_host_pipeline_equals_device_step(N, G, n, copy_obs):
             assert torch.equal(obs.cpu().view(torch.int32), h_obs.view(torch.int32))
 
 
+@pytest.mark.parametrize('G,n,r,extra,N', [(9, 4, 3, {}, 100003), (8, 3, 3, {}, 90001),
+                                           (64, 32, 5, {'stations_factor': 8, 'skyscrapers_factor': 16}, 3001)])
+def test_ticket_order_equals_static_order(monkeypatch, G, n, r, extra, N):
+    """The step kernels hand their env groups out through a device-wide ticket counter (time order keeps the obs
+    stream's DRAM locality).  Which worker steps which env must not matter: same results, bit for bit, as the static
+    grid-stride order (DRL_STATIC_ORDER=1, read when a handle is created), over several launches (the last worker
+    out re-arms the counters) and with more groups than resident workers."""
+    import dronerl_b200 as drl
+    p = drl.DroneEnvParams(grid_size=G, n_drones=n, window_radius=r, **extra)
+    key = drl.random.PRNGKey(11)
+    env_t = drl.DeliveryDrones()
+    a = env_t.reset(key, p, num_envs=N)
+    monkeypatch.setenv('DRL_STATIC_ORDER', '1')
+    env_s = drl.DeliveryDrones()
+    b = env_s.reset(key, p, num_envs=N)
+    monkeypatch.delenv('DRL_STATIC_ORDER')
+    assert torch.equal(a.ground_raw, b.ground_raw) and torch.equal(a.drones_raw, b.drones_raw)
+    for t in range(5):
+        acts = torch.from_numpy(np.random.default_rng(t).integers(0, 5, size=(N, n)).astype(np.int8)).cuda()
+        k = drl.random.PRNGKey(300 + t)
+        monkeypatch.setenv('DRL_STATIC_ORDER', '1')     # (handles are cached per env object; this only guards re-creation)
+        b, rew_s, done_s, obs_s = env_s.step(k, b, acts, p, return_obs=True)
+        monkeypatch.delenv('DRL_STATIC_ORDER')
+        a, rew_t, done_t, obs_t = env_t.step(k, a, acts, p, return_obs=True)
+        assert torch.equal(a.ground_raw, b.ground_raw) and torch.equal(a.drones_raw, b.drones_raw), f'state differs at step {t}'
+        assert torch.equal(rew_t.view(torch.int32), rew_s.view(torch.int32)) and torch.equal(done_t, done_s)
+        assert torch.equal(obs_t.view(torch.int32), obs_s.view(torch.int32)), f'obs differ at step {t}'
+    assert env_t.stats(a, p) == env_s.stats(b, p)
+
+
+@pytest.mark.timeout(180)
+@pytest.mark.parametrize('N', [999, 70001])
+def test_step_host_with_pageable_host_buffers(N):
+    """drl_step_host with ordinary (not page-locked) host memory: the copies serialise, the results are the same."""
+    import ctypes
+    import dronerl_b200 as drl
+    from dronerl_b200 import _lib
+    from dronerl_b200.env import _vp, _stream
+    n = 4
+    p = drl.DroneEnvParams(grid_size=9, n_drones=n)
+    env = drl.DeliveryDrones()
+    a = env.reset(drl.random.PRNGKey(2), p, num_envs=N)
+    b = a.clone()
+    W = p.window_size
+    for t in range(2):
+        acts = np.random.default_rng(t).integers(0, 5, size=(N, n)).astype(np.int8)
+        key = drl.random.PRNGKey(70 + t)
+        a, rew, done, obs = env.step(key, a, torch.from_numpy(acts).cuda(), p, return_obs=True)
+        h = env._state_handle(b, p)
+        h_rew = np.empty((N, n), dtype=np.float32)
+        h_done = np.empty((N, n), dtype=np.uint8)
+        d_obs = torch.empty((N, n, W, W, 6), dtype=torch.float32, device='cuda')
+        h.check(h.lib.drl_step_host(h.ptr, _lib.key_array(key), ctypes.c_void_p(acts.ctypes.data),
+                                    ctypes.c_void_p(h_rew.ctypes.data), ctypes.c_void_p(h_done.ctypes.data), _vp(d_obs),
+                                    ctypes.c_void_p(0), _stream()))
+        assert torch.equal(a.ground_raw, b.ground_raw) and torch.equal(a.drones_raw, b.drones_raw)
+        np.testing.assert_array_equal(rew.cpu().numpy().view(np.uint32), h_rew.view(np.uint32))
+        np.testing.assert_array_equal(done.cpu().numpy().view(np.uint8), h_done)
+        assert torch.equal(obs.view(torch.int32), d_obs.view(torch.int32))
+
+
 @pytest.mark.parametrize('G,n,r,N,off,Ng', [(9, 4, 3, 5000, 0, 5000), (8, 3, 3, 3001, 7000, 16001), (11, 20, 1, 300, 50, 400),
                                             (12, 6, 4, 700, 100, 900), (64, 32, 5, 24, 8, 40)])
 def test_step_keyed_equals_explicit_keys_and_actions(c_oracle, G, n, r, N, off, Ng):
