@@ -71,6 +71,90 @@ __global__ void __launch_bounds__(256, 3) k_store(float* __restrict__ out, long 
     if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }
 
+// Group form (what the step kernel does since it draws tickets): a warp takes 8 consecutive records per turn -- their
+// state rows read together one group ahead, their tiles stored one after the other, their state written back together.
+// order 0: static grid-stride groups; 1: groups drawn from a ticket counter (one ahead of the prefetch).
+__device__ unsigned g_tickets[2];
+__global__ void __launch_bounds__(256, 3) k_group(float* __restrict__ out, long long nrec, uint4* __restrict__ ground, uint32_t* __restrict__ drones,
+                                                  float* __restrict__ rewards, unsigned char* __restrict__ dones, const uint2* __restrict__ keys,
+                                                  const int* __restrict__ actions, int small, int order, int hint) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    constexpr int S = 4704, Q = 8;
+    // hint 1: state loads / stores carry an L2 evict_last policy, tile stores evict_first (with the persisting L2
+    // carve-out set by the host): does the 117 MB of state survive in L2 from one launch to the next?
+    unsigned long long pol_last = 0, pol_first = 0;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_last));
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_first));
+    auto ldg4 = [&](const uint4* p) {
+        uint4 v;
+        if (hint) asm volatile("ld.global.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p), "l"(pol_last));
+        else v = *p;
+        return v;
+    };
+    auto stg4 = [&](uint4* p, uint4 v) {
+        if (hint) asm volatile("st.global.L2::cache_hint.v4.u32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "l"(pol_last) : "memory");
+        else *p = v;
+    };
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int bufsz = (S + 127) / 128 * 128;
+    float4* buf = reinterpret_cast<float4*>(smem + (size_t)warp * bufsz);
+    for (int i = lane; i < bufsz / 16; i += 32) buf[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    __syncwarp();
+    const long long nw = (long long)gridDim.x * 8, w0 = (long long)blockIdx.x * 8 + warp, ngroups = nrec / Q;
+    const uint32_t saddr = (uint32_t)__cvta_generic_to_shared(buf);
+    auto ticket = [&](long long after) -> long long {
+        if (!order) return after + nw;
+        unsigned t = 0;
+        if (lane == 0) t = atomicAdd(&g_tickets[0], 1u);
+        return nw + (long long)__shfl_sync(0xFFFFFFFFu, t, 0);
+    };
+    uint4 ng0 = make_uint4(0, 0, 0, 0), ng1 = ng0; uint32_t ndr = 0; int nac = 0; uint2 nkk = make_uint2(0, 0);
+    auto prefetch = [&](long long g) {
+        if (g < ngroups && (small & 1)) {
+            const long long e0 = g * Q;
+            ng0 = ldg4(ground + e0 * 6 + lane);                // 8 rows x 6 vectors = 48 vectors
+            if (lane < 16) ng1 = ldg4(ground + e0 * 6 + 32 + lane);
+            ndr = drones[e0 * 4 + lane];                       // 8 envs x 4 drones
+            if (lane < 8) { nac = actions[e0 + lane]; nkk = keys[e0 + lane]; }
+        }
+    };
+    long long g = w0;
+    prefetch(g);
+    long long gn = ticket(g), gnn = 0;
+    for (; g < ngroups; g = gn, gn = gnn) {
+        const uint4 g0 = ng0, g1 = ng1; const uint32_t dr = ndr; const int ac = nac; const uint2 kk = nkk;
+        prefetch(gn);
+        gnn = ticket(gn);
+        const long long e0 = g * Q;
+        for (int q = 0; q < Q; ++q) {
+            if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            __syncwarp();
+            for (int t = 0; t < 8; ++t) buf[(lane + 32 * t) % (bufsz / 16)] = make_float4((float)(g0.x + g1.y + dr + ac + kk.x + q), 0.f, 0.f, 0.f);
+            if (q == 0 && (small & 2)) {
+                uint4 a = g0, b = g1; a.x ^= 1u; b.x ^= 1u;
+                stg4(ground + e0 * 6 + lane, a);
+                if (lane < 16) stg4(ground + e0 * 6 + 32 + lane, b);
+                drones[e0 * 4 + lane] = dr + 1u;
+                rewards[e0 * 4 + lane] = 1.0f;
+                if (lane < 8) reinterpret_cast<uint32_t*>(dones)[e0 + lane] = 0x01010101u;
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) {
+                char* dst = reinterpret_cast<char*>(out) + (e0 + q) * (long long)S;
+                if (hint) asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(dst), "r"(saddr), "r"(S), "l"(pol_first) : "memory");
+                else asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(saddr), "r"(S) : "memory");
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+        }
+    }
+    if (lane == 0) {
+        asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+        __threadfence();
+        if (atomicAdd(&g_tickets[1], 1u) == (unsigned)(nw - 1)) { g_tickets[0] = 0u; g_tickets[1] = 0u; }
+    }
+}
+
 int main() {
     const long long nrec = 1 << 20;
     float* out;
@@ -81,6 +165,49 @@ int main() {
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0);
     cudaEventCreate(&e1);
+    {
+        const int smem = 8 * 4736;
+        cudaFuncSetAttribute(k_group, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        cudaDeviceProp prop;
+        cudaGetDeviceProperties(&prop, 0);
+        printf("persistingL2CacheMaxSize %d MB, accessPolicyMaxWindowSize %d MB, L2 %d MB\n", prop.persistingL2CacheMaxSize >> 20,
+               prop.accessPolicyMaxWindowSize >> 20, prop.l2CacheSize >> 20);
+        cudaStream_t st;
+        cudaStreamCreate(&st);
+        // variant: 0 plain, 1 PTX cache hints, 2 hints + persisting carve-out, 3 carve-out + stream access-policy window on the ground
+        for (int variant = 0; variant < 4; ++variant) {
+            if (variant == 2) cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, prop.persistingL2CacheMaxSize);
+            if (variant == 3) {
+                cudaStreamAttrValue av = {};
+                av.accessPolicyWindow.base_ptr = ground;
+                size_t win = (size_t)nrec * 96;
+                if (win > (size_t)prop.accessPolicyMaxWindowSize) win = prop.accessPolicyMaxWindowSize;
+                av.accessPolicyWindow.num_bytes = win;
+                av.accessPolicyWindow.hitRatio = (float)((double)prop.persistingL2CacheMaxSize * 0.9 / (double)win);
+                if (av.accessPolicyWindow.hitRatio > 1.f) av.accessPolicyWindow.hitRatio = 1.f;
+                av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+                av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+                printf("window %zu MB hitRatio %.2f: %s\n", win >> 20, av.accessPolicyWindow.hitRatio,
+                       cudaGetErrorString(cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &av)));
+            }
+            const int hint = (variant == 1 || variant == 2) ? 1 : 0;
+            for (int small = 0; small < 4; small += 3) {
+                const int order = 1;
+                for (int rep = 0; rep < 3; ++rep) k_group<<<444, 256, smem, st>>>(out, nrec, ground, drones, rewards, dones, keys, actions, small, order, hint);
+                cudaEventRecord(e0, st);
+                for (int rep = 0; rep < 5; ++rep) k_group<<<444, 256, smem, st>>>(out, nrec, ground, drones, rewards, dones, keys, actions, small, order, hint);
+                cudaEventRecord(e1, st);
+                cudaEventSynchronize(e1);
+                float ms;
+                cudaEventElapsedTime(&ms, e0, e1);
+                ms /= 5;
+                printf("variant %d, groups of 8, tickets, state %s: %.3f ms  %.0f GB/s tile stream  (%s)\n", variant, small ? "RW" : "--", ms,
+                       (double)nrec * 4704 / ms / 1e6, cudaGetErrorString(cudaGetLastError()));
+            }
+        }
+        cudaCtxResetPersistingL2Cache();
+        return 0;
+    }
     const int sizes[] = {4704};
     for (int GV : {6, 3, 2}) for (int small : {6}) for (int touch : {8}) {
         for (int S : sizes) {
