@@ -154,6 +154,23 @@ def test_step_host_pipeline_equals_device_step(N, G, n, copy_obs):
             assert torch.equal(obs.cpu().view(torch.int32), h_obs.view(torch.int32))
 
 
+@pytest.mark.parametrize('total,first,count', [(20001, 0, 20001), (20001, 0, 7000), (20001, 12000, 8001), (20001, 6000, 9000),
+                                               (20000, 9999, 2), (20000, 10000, 10000), (1, 0, 1), (3, 1, 2)])
+def test_split_and_randint_slices_match_oracle(c_oracle, total, first, count):
+    """The derivation kernels walk threefry blocks (one hash serves elements b and half + b): every kind of local
+    slice -- whole vector, inside the first half, inside the second half, straddling the middle, odd totals with the
+    zero pad counter -- equals the slice of the oracle's jax.random.split / randint (train_jax.py:44,53)."""
+    import dronerl_b200 as drl
+    C = c_oracle
+    key = drl.random.PRNGKey(1234)
+    want_k = C.split(key, total)[first:first + count]
+    got_k = drl.random.split(key, total, offset=first, count=count).cpu().numpy()
+    np.testing.assert_array_equal(got_k, want_k)
+    want_a = C.randint(key, total, 0, 5)[first:first + count]
+    got_a = drl.random.randint(key, (total,), 0, 5, first=first, count=count).cpu().numpy().reshape(-1)
+    np.testing.assert_array_equal(got_a.astype(np.int64), np.asarray(want_a).astype(np.int64))
+
+
 @pytest.mark.parametrize('G,n,r,extra,N', [(9, 4, 3, {}, 100003), (8, 3, 3, {}, 90001),
                                            (64, 32, 5, {'stations_factor': 8, 'skyscrapers_factor': 16}, 3001)])
 def test_ticket_order_equals_static_order(monkeypatch, G, n, r, extra, N):

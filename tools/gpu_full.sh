@@ -11,3 +11,4 @@ timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --c
 # ncu --set full captures of the dominant kernels at the bench shapes (DRAM traffic per launch -> profiles/step_kernel_traffic.json)
 timeout 300 ncu --set full --import-source on --clock-control none -k regex:k_step_warp -s 5 -c 1 -o gpurun_out/step_warp_full -f python bench.py --steps 8 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/ncu_warp_full.log 2>&1; echo "ncu warp rc=$?"
 timeout 400 ncu --set full --import-source on --clock-control none -k regex:k_step_ -s 6 -c 2 -o gpurun_out/step_c4_full -f python bench.py --grid 64 --drones 32 --radius 5 --stations-factor 8 --skyscrapers-factor 16 --envs-per-gpu 262144 --steps 4 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/ncu_c4_full.log 2>&1; echo "ncu c4 rc=$?"
+timeout 200 python tools/bench_c5.py --steps 1000 --warmup 100 > gpurun_out/c5_n1.json 2> gpurun_out/c5_n1.err; echo "c5 rc=$?"; tail -c 400 gpurun_out/c5_n1.json

@@ -77,8 +77,9 @@ __global__ void __launch_bounds__(256, 3) k_store(float* __restrict__ out, long 
 __device__ unsigned g_tickets[2];
 __global__ void __launch_bounds__(256, 3) k_group(float* __restrict__ out, long long nrec, uint4* __restrict__ ground, uint32_t* __restrict__ drones,
                                                   float* __restrict__ rewards, unsigned char* __restrict__ dones, const uint2* __restrict__ keys,
-                                                  const int* __restrict__ actions, int small, int order, int hint) {
+                                                  const int* __restrict__ actions, int small, int order, int hint, int layout = 0) {
     extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ unsigned s_ticket;
     constexpr int S = 4704, Q = 8;
     // hint 1: state loads / stores carry an L2 evict_last policy, tile stores evict_first (with the persisting L2
     // carve-out set by the host): does the 117 MB of state survive in L2 from one launch to the next?
@@ -102,11 +103,20 @@ __global__ void __launch_bounds__(256, 3) k_group(float* __restrict__ out, long 
     __syncwarp();
     const long long nw = (long long)gridDim.x * 8, w0 = (long long)blockIdx.x * 8 + warp, ngroups = nrec / Q;
     const uint32_t saddr = (uint32_t)__cvta_generic_to_shared(buf);
+    // layout 0: every warp draws its own group of 8 consecutive records.  1 / 2: the CTA draws 64 consecutive records
+    // (barrier per turn); warp w takes records 8w .. 8w+7 of them (1) or w, w+8, .. (2: the CTA's eight warps write
+    // eight neighbouring tiles at the same time).  Group ids are then in units of warps' turns: g = 8 * cta_ticket + w.
     auto ticket = [&](long long after) -> long long {
         if (!order) return after + nw;
-        unsigned t = 0;
-        if (lane == 0) t = atomicAdd(&g_tickets[0], 1u);
-        return nw + (long long)__shfl_sync(0xFFFFFFFFu, t, 0);
+        if (layout == 0) {
+            unsigned t = 0;
+            if (lane == 0) t = atomicAdd(&g_tickets[0], 1u);
+            return nw + (long long)__shfl_sync(0xFFFFFFFFu, t, 0);
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) s_ticket = atomicAdd(&g_tickets[0], 1u);
+        __syncthreads();
+        return nw + (long long)s_ticket * 8 + warp;
     };
     uint4 ng0 = make_uint4(0, 0, 0, 0), ng1 = ng0; uint32_t ndr = 0; int nac = 0; uint2 nkk = make_uint2(0, 0);
     auto prefetch = [&](long long g) {
@@ -126,6 +136,7 @@ __global__ void __launch_bounds__(256, 3) k_group(float* __restrict__ out, long 
         prefetch(gn);
         gnn = ticket(gn);
         const long long e0 = g * Q;
+        const long long cta0 = (g - warp) * Q;               // layout 2: first record of the CTA's 64
         for (int q = 0; q < Q; ++q) {
             if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
             __syncwarp();
@@ -141,7 +152,8 @@ __global__ void __launch_bounds__(256, 3) k_group(float* __restrict__ out, long 
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncwarp();
             if (lane == 0) {
-                char* dst = reinterpret_cast<char*>(out) + (e0 + q) * (long long)S;
+                const long long rec = layout == 2 ? cta0 + q * 8 + warp : e0 + q;
+                char* dst = reinterpret_cast<char*>(out) + rec * (long long)S;
                 if (hint) asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(dst), "r"(saddr), "r"(S), "l"(pol_first) : "memory");
                 else asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(saddr), "r"(S) : "memory");
                 asm volatile("cp.async.bulk.commit_group;" ::: "memory");
@@ -174,6 +186,20 @@ int main() {
                prop.accessPolicyMaxWindowSize >> 20, prop.l2CacheSize >> 20);
         cudaStream_t st;
         cudaStreamCreate(&st);
+        for (int layout = 0; layout < 3; ++layout)
+            for (int small = 0; small < 4; small += 3) {
+                for (int rep = 0; rep < 3; ++rep) k_group<<<444, 256, smem, st>>>(out, nrec, ground, drones, rewards, dones, keys, actions, small, 1, 0, layout);
+                cudaEventRecord(e0, st);
+                for (int rep = 0; rep < 5; ++rep) k_group<<<444, 256, smem, st>>>(out, nrec, ground, drones, rewards, dones, keys, actions, small, 1, 0, layout);
+                cudaEventRecord(e1, st);
+                cudaEventSynchronize(e1);
+                float ms;
+                cudaEventElapsedTime(&ms, e0, e1);
+                ms /= 5;
+                printf("layout %d (0 warp tickets, 1 CTA tickets blocked, 2 CTA tickets interleaved), state %s: %.3f ms  %.0f GB/s tile stream  (%s)\n", layout,
+                       small ? "RW" : "--", ms, (double)nrec * 4704 / ms / 1e6, cudaGetErrorString(cudaGetLastError()));
+            }
+        if (getenv("STATE_MIX_L2")) {
         // variant: 0 plain, 1 PTX cache hints, 2 hints + persisting carve-out, 3 carve-out + stream access-policy window on the ground
         for (int variant = 0; variant < 4; ++variant) {
             if (variant == 2) cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, prop.persistingL2CacheMaxSize);
@@ -204,6 +230,7 @@ int main() {
                 printf("variant %d, groups of 8, tickets, state %s: %.3f ms  %.0f GB/s tile stream  (%s)\n", variant, small ? "RW" : "--", ms,
                        (double)nrec * 4704 / ms / 1e6, cudaGetErrorString(cudaGetLastError()));
             }
+        }
         }
         cudaCtxResetPersistingL2Cache();
         return 0;
