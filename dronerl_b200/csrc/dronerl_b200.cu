@@ -89,7 +89,7 @@ k_reset_warp(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uin
 template <class D>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 k_obs_warp(const __grid_constant__ DevCfg c, const uint8_t* __restrict__ ground, const uint32_t* __restrict__ drones,
-           float* __restrict__ obs) {
+           float* __restrict__ obs, unsigned* __restrict__ queue) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     unsigned char* base = smem_raw + (size_t)warp * c.group_bytes;
@@ -98,16 +98,33 @@ k_obs_warp(const __grid_constant__ DevCfg c, const uint8_t* __restrict__ ground,
     int tsel = 0;
     const D d{c};
     const int nvec = d.GS() >> 4, n = d.n();
-    const long long stride = (long long)gridDim.x * kWarpsPerBlock;
-    for (long long e = (long long)blockIdx.x * kWarpsPerBlock + warp; e < c.N; e += stride) {
-        __syncwarp();
-        if (lane < nvec) reinterpret_cast<uint4*>(sm.sg)[lane] = reinterpret_cast<const uint4*>(ground + e * d.GS())[lane];
-        const uint32_t rec = lane < n ? drones[e * n + lane] : 0u;
-        obs_publish(d, sm, lane, rec);
-        __syncwarp();
-        obs_tiles(d, c, sm, obs, e, tile, tsel, 0, 1, lane);
+    // batches of 8 consecutive envs per warp, drawn from a ticket counter after the first one (time-ordered addresses
+    // keep the tile stream's DRAM locality, see step_warp.cuh); queue == nullptr: static order
+    const long long total_warps = (long long)gridDim.x * kWarpsPerBlock, nbatch = (c.N + 7) >> 3;
+    auto ticket = [&](long long after) -> long long {
+        if (queue == nullptr) return after + total_warps;
+        unsigned t = 0;
+        if (lane == 0) t = atomicAdd(queue, 1u);
+        return total_warps + (long long)__shfl_sync(FULL, t, 0);
+    };
+    long long b = (long long)blockIdx.x * kWarpsPerBlock + warp;
+    long long bn = ticket(b);
+    for (; b < nbatch; b = bn, bn = ticket(b)) {
+        const long long e1 = min(c.N, (b + 1) << 3);
+        for (long long e = b << 3; e < e1; ++e) {
+            __syncwarp();
+            if (lane < nvec) reinterpret_cast<uint4*>(sm.sg)[lane] = reinterpret_cast<const uint4*>(ground + e * d.GS())[lane];
+            const uint32_t rec = lane < n ? drones[e * n + lane] : 0u;
+            obs_publish(d, sm, lane, rec);
+            __syncwarp();
+            obs_tiles(d, c, sm, obs, e, tile, tsel, 0, 1, lane);
+        }
     }
     tile_drain(lane);
+    if (queue != nullptr && lane == 0) {
+        __threadfence();
+        if (atomicAdd(queue + 1, 1u) == (unsigned)(total_warps - 1)) { queue[0] = 0u; queue[1] = 0u; }
+    }
 }
 
 // ---- CTA-per-env kernels (larger grids) -------------------------------------------------------
@@ -314,7 +331,7 @@ k_reset_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint
 template <class D>
 __global__ void __launch_bounds__(kCtaThreads)
 k_obs_cta(const __grid_constant__ DevCfg c, const uint8_t* __restrict__ ground, const uint32_t* __restrict__ drones,
-          float* __restrict__ obs) {
+          float* __restrict__ obs, unsigned* __restrict__ queue) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     constexpr int T = kCtaThreads;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -323,8 +340,16 @@ k_obs_cta(const __grid_constant__ DevCfg c, const uint8_t* __restrict__ ground, 
     int tsel = 0;
     const D d{c};
     const int nvec = c.GS >> 4, n = c.n;
-    for (long long e = blockIdx.x; e < c.N; e += gridDim.x) {
+    // envs drawn from a ticket counter after the first one, one env ahead (thread 0; published through misc[10])
+    unsigned tk = 0;
+    if (queue != nullptr && threadIdx.x == 0) tk = atomicAdd(queue, 1u);
+    long long en = 0;
+    for (long long e = blockIdx.x; e < c.N; e = en) {
         __syncthreads();
+        if (queue != nullptr && threadIdx.x == 0) {
+            sm.misc[10] = tk;
+            tk = atomicAdd(queue, 1u);
+        }
         for (int i = threadIdx.x; i < nvec; i += T)
             reinterpret_cast<uint4*>(sm.sg)[i] = reinterpret_cast<const uint4*>(ground + e * c.GS)[i];
         if (warp == 0) {
@@ -332,9 +357,14 @@ k_obs_cta(const __grid_constant__ DevCfg c, const uint8_t* __restrict__ ground, 
             obs_publish(d, sm, lane, rec);
         }
         __syncthreads();
+        en = queue != nullptr ? (long long)gridDim.x + (long long)sm.misc[10] : e + gridDim.x;
         obs_tiles(d, c, sm, obs, e, tile, tsel, warp, T / 32, lane);
     }
     tile_drain(lane);
+    if (queue != nullptr && threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(queue + 1, 1u) == gridDim.x - 1u) { queue[0] = 0u; queue[1] = 0u; }
+    }
 }
 
 // ---- key / action derivation --------------------------------------------------------------------
@@ -470,7 +500,7 @@ typedef void (*step_fn)(DevCfg, uint8_t*, uint32_t*, const uint32_t*, const int8
                         unsigned long long*);
 
 typedef void (*reset_fn)(DevCfg, uint8_t*, uint32_t*, const uint32_t*, unsigned long long*);
-typedef void (*obs_fn)(DevCfg, const uint8_t*, const uint32_t*, float*);
+typedef void (*obs_fn)(DevCfg, const uint8_t*, const uint32_t*, float*, unsigned*);
 
 using D943 = Dims<9, 4, 3>;    // train_jax.py CLI defaults (train_jax.py:338-344)
 using D833 = Dims<8, 3, 3>;    // DroneEnvParams dataclass defaults (jax_impl/env/env.py:13-26)
@@ -791,9 +821,9 @@ int drl_create(const drl_config* cfg, drl_env** out) {
         return DRL_ECUDA;
     }
     // statistics block + 16 bytes of key scratch for the *_dev entry points
-    // + 16 ticket-counter pairs (one per concurrent launch slot) for the step kernels' dynamic env order
-    if (cudaMalloc(&e->d_stats, (DRL_NUM_STATS + 2 + 16) * sizeof(unsigned long long)) != cudaSuccess ||
-        cudaMemset(e->d_stats, 0, (DRL_NUM_STATS + 2 + 16) * sizeof(unsigned long long)) != cudaSuccess) {
+    // + 17 ticket-counter pairs (one per concurrent step launch slot, the last one for the obs kernel)
+    if (cudaMalloc(&e->d_stats, (DRL_NUM_STATS + 2 + 17) * sizeof(unsigned long long)) != cudaSuccess ||
+        cudaMemset(e->d_stats, 0, (DRL_NUM_STATS + 2 + 17) * sizeof(unsigned long long)) != cudaSuccess) {
         delete e;
         return fail(nullptr, DRL_ECUDA, "cudaMalloc of the statistics block failed%s");
     }
@@ -994,8 +1024,9 @@ int drl_get_obs(drl_env* env, void* d_obs, void* stream) {
     if ((uintptr_t)d_obs & 7) return fail(env, DRL_EINVAL, "drl_get_obs: obs must be 8-byte aligned%s");
     CUDA_TRY(env, cudaSetDevice(env->cfg.device));
     const int threads = env->warp_mode ? kWarpsPerBlock * 32 : kCtaThreads;
+    unsigned* queue = env->static_order ? nullptr : reinterpret_cast<unsigned*>(env->d_stats + DRL_NUM_STATS + 2) + 2 * 16;
     return launch(env, "obs kernel", (const void*)pick_obs(env), env->grid_obs, threads, env->smem_bytes, stream, env->dc,
-                  (const uint8_t*)env->d_ground, (const uint32_t*)env->d_drones, (float*)d_obs);
+                  (const uint8_t*)env->d_ground, (const uint32_t*)env->d_drones, (float*)d_obs, queue);
 }
 
 static int ensure_scratch(drl_env* env) {
