@@ -113,6 +113,60 @@ def fuzz(num_envs=6, steps=40):
     return total
 
 
+ALIAS_SHAPES = [
+    dict(grid_size=4, n_drones=4, window_radius=1, packets_factor=1, dropzones_factor=1, stations_factor=0, skyscrapers_factor=0),
+    dict(grid_size=5, n_drones=6, window_radius=2, packets_factor=1, dropzones_factor=1, stations_factor=0, skyscrapers_factor=0),
+    dict(grid_size=6, n_drones=8, window_radius=1, packets_factor=1, dropzones_factor=1, stations_factor=1, skyscrapers_factor=0),
+    dict(grid_size=8, n_drones=3, window_radius=3),
+]
+
+
+def fuzz_alias(num_envs=10, steps=60):
+    """Directed stress of the scatter-aliasing rule (SURVEY.md 8a S9 caveat): actions biased towards LEFT / UP on
+    small crowded grids, so drones keep leaving by the top / left edge and their index -1 wraps onto the last row /
+    column, where other drones pick up and deliver.  Returns (env-steps compared, index-alias events, events where
+    the aliasing drone's update differs from a lower-indexed drone's pickup / delivery removal at the same cell)."""
+    from oracle import env_ref as E
+    from oracle import jaxrand as jr
+    env = DeliveryDrones()
+    total = alias = conflict = 0
+    for si, cfg in enumerate(ALIAS_SHAPES):
+        p, op = DroneEnvParams(**cfg), E.Params(**cfg)
+        G, n = op.grid_size, op.n_drones
+        rng = np.random.default_rng(700 + si)
+        keys = jr.split(jr.PRNGKey(90 + si), num_envs)
+        for e in range(num_envs):
+            s, o = env.reset(jax.numpy.array(keys[e]), p), E.reset(keys[e], op)
+            for t in range(steps):
+                for f, v in state_arrays(s).items():
+                    same(v, getattr(o, f), f'alias shape {si} env {e} step {t} {f}')
+                k = jr.split(jr.PRNGKey(5000 * si + 70 * e + t), 2)[1]
+                acts = rng.choice(5, size=n, p=[0.35, 0.1, 0.1, 0.35, 0.1]).astype(np.int32)   # LEFT0 DOWN1 RIGHT2 UP3 STAY4
+                # bookkeeping on the oracle's state: who aliases whom this step
+                dx = (acts == 2).astype(int) - (acts == 0).astype(int)
+                dy = (acts == 1).astype(int) - (acts == 3).astype(int)
+                nx, ny = np.asarray(o.air_x) + dx, np.asarray(o.air_y) + dy
+                ground = np.asarray(o.ground)
+                carry = np.asarray(o.carrying_package)
+                for j in range(n):
+                    if (nx[j] == -1 or ny[j] == -1) and nx[j] < G and ny[j] < G:
+                        cj = (ny[j] % G, nx[j] % G)
+                        for i in range(j):
+                            if 0 <= nx[i] < G and 0 <= ny[i] < G and (ny[i], nx[i]) == cj:
+                                alias += 1
+                                cell = ground[ny[i], nx[i]]
+                                if (cell == 5 and not carry[i]) or (cell == 4 and carry[i]):
+                                    conflict += 1
+                s, rew, done = env.step(jax.numpy.array(k), s, jax.numpy.array(acts), p)
+                o, orew, odone = E.step(k, o, acts, op)
+                same(rew, orew, f'alias shape {si} env {e} step {t} rewards')
+                same(done, odone, f'alias shape {si} env {e} step {t} dones')
+                same(env.get_obs(s, p), E.get_obs(o, op), f'alias shape {si} env {e} step {t} obs')
+                total += 1
+        print(f'alias shape {si} {cfg}: identical ({alias} index-alias events, {conflict} with a pickup/delivery at the aliased cell so far)')
+    return total, alias, conflict
+
+
 def main():
     if not os.path.isdir(os.path.join(REF, 'jax_impl')):
         raise SystemExit(f'{REF} not found: this check runs where the reference checkout exists')
@@ -127,6 +181,9 @@ def main():
     manifest['fixtures']['prng.npz'] = {'sha256': hashlib.sha256(open(os.path.join(HERE, 'prng.npz'), 'rb').read()).hexdigest(),
                                         'env_steps_replayed': 0}
     manifest['fuzz_env_steps_identical_to_oracle'] = fuzz()
+    at, aa, ac = fuzz_alias()
+    manifest['alias_stress'] = {'env_steps_identical_to_oracle': at, 'index_alias_events': aa,
+                                'alias_events_at_a_pickup_or_delivery_cell': ac}
     with open(os.path.join(HERE, 'reference_source_check.json'), 'w') as f:
         json.dump(manifest, f, indent=1)
     print('wrote reference_source_check.json')
