@@ -76,6 +76,44 @@ def test_rollout_matches_oracle(c_oracle, G, n, r, extra, N, steps):
             assert_state_equal(state, ostate, f'reset at {t}')
 
 
+ALIAS_CONFIGS = [
+    (4, 4, 1, {'packets_factor': 1, 'dropzones_factor': 1, 'stations_factor': 0, 'skyscrapers_factor': 0}),
+    (5, 6, 2, {'packets_factor': 1, 'dropzones_factor': 1, 'stations_factor': 0, 'skyscrapers_factor': 0}),
+    (6, 8, 1, {'packets_factor': 1, 'dropzones_factor': 1, 'stations_factor': 1, 'skyscrapers_factor': 0}),
+    (8, 3, 3, {}),
+    (14, 12, 2, {'packets_factor': 2, 'dropzones_factor': 2, 'stations_factor': 0, 'skyscrapers_factor': 0}),   # CTA mode
+]
+
+
+@pytest.mark.parametrize('G,n,r,extra', ALIAS_CONFIGS)
+def test_scatter_aliasing_stress_matches_oracle(c_oracle, G, n, r, extra):
+    """Actions biased towards LEFT / UP on small crowded grids: drones keep leaving by the top / left edge, their index
+    -1 wraps onto the last row / column where other drones pick up and deliver, and the last scatter update per cell
+    must win (SURVEY.md 8a S9 caveat; same stress as tests/golden/verify_against_reference_source.py::fuzz_alias,
+    which runs the reference's own source)."""
+    import dronerl_b200 as drl
+    C = c_oracle
+    N, steps = 2048, 48
+    p = drl.DroneEnvParams(grid_size=G, n_drones=n, window_radius=r, **extra)
+    op = oracle_params(p)
+    env = drl.DeliveryDrones()
+    rng = np.random.default_rng(G * 31 + n)
+    reset_keys = C.split(drl.random.PRNGKey(G + 100 * n), N)
+    state = env.reset(torch.from_numpy(reset_keys).cuda(), p)
+    ostate = C.reset(reset_keys, op)
+    for t in range(steps):
+        acts = rng.choice(5, size=(N, n), p=[0.35, 0.1, 0.1, 0.35, 0.1]).astype(np.int32)   # LEFT0 DOWN1 RIGHT2 UP3 STAY4
+        keys = C.split(drl.random.PRNGKey(3000 + t), N)
+        out = env.step(torch.from_numpy(keys).cuda(), state, torch.from_numpy(acts).cuda(), p, return_obs=(t % 8 == 0))
+        orew, odone = C.step(keys, ostate, acts, op)
+        assert_state_equal(out[0], ostate, f'step {t}')
+        np.testing.assert_array_equal(out[2].cpu().numpy(), odone, err_msg=f'dones step {t}')
+        np.testing.assert_array_equal(out[1].cpu().numpy().view(np.uint32), orew.view(np.uint32), err_msg=f'rewards step {t}')
+        if t % 8 == 0:
+            np.testing.assert_array_equal(out[3].cpu().numpy().view(np.uint32), C.get_obs(ostate, op).view(np.uint32),
+                                          err_msg=f'obs step {t}')
+
+
 def test_parent_key_split_matches_explicit_keys(c_oracle):
     """step(key(2,), ...) on a batched state == vmap(step)(split(key, N), ...)  (train_jax.py:52-54)."""
     import dronerl_b200 as drl
