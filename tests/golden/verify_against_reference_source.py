@@ -167,6 +167,33 @@ def fuzz_alias(num_envs=10, steps=60):
     return total, alias, conflict
 
 
+def tie_cases():
+    """The frozen top_k tie keys (tie_keys.json, find_tie_keys.py) through the reference source: same respawns as the oracle."""
+    from oracle import env_ref as E
+    from oracle import jaxrand as jr
+    import find_tie_keys as F
+    env = DeliveryDrones()
+    cases = json.load(open(os.path.join(HERE, 'tie_keys.json')))
+    total = 0
+    for name, c in cases.items():
+        p, op = DroneEnvParams(**c['params']), E.Params(**c['params'])
+        _, s0, acts, _, _ = F.air_setup(c['params'], c['reset_seed'], c['action_seed'])
+        rs = env.reset(jax.numpy.array(jr.PRNGKey(c['reset_seed'])), p)
+        for f, v in state_arrays(rs).items():
+            same(v, getattr(s0, f), f'tie case {name}: reset {f}')
+        for kk in c['step_keys']:
+            key = np.array(kk, dtype=np.uint32)
+            s, rew, done = env.step(jax.numpy.array(key), rs, jax.numpy.array(acts), p)
+            o, orew, odone = E.step(key, s0.copy(), acts, op)
+            for f, v in state_arrays(s).items():
+                same(v, getattr(o, f), f'tie case {name} key {kk}: {f}')
+            same(rew, orew, f'tie case {name} key {kk}: rewards')
+            same(done, odone, f'tie case {name} key {kk}: dones')
+            total += 1
+        print(f'tie case {name}: {len(c["step_keys"])} tied steps identical')
+    return total
+
+
 def main():
     if not os.path.isdir(os.path.join(REF, 'jax_impl')):
         raise SystemExit(f'{REF} not found: this check runs where the reference checkout exists')
@@ -181,6 +208,7 @@ def main():
     manifest['fixtures']['prng.npz'] = {'sha256': hashlib.sha256(open(os.path.join(HERE, 'prng.npz'), 'rb').read()).hexdigest(),
                                         'env_steps_replayed': 0}
     manifest['fuzz_env_steps_identical_to_oracle'] = fuzz()
+    manifest['top_k_tie_steps_identical_to_oracle'] = tie_cases()
     at, aa, ac = fuzz_alias()
     manifest['alias_stress'] = {'env_steps_identical_to_oracle': at, 'index_alias_events': aa,
                                 'alias_events_at_a_pickup_or_delivery_cell': ac}

@@ -152,3 +152,51 @@ def test_cuda_prng_reproduces_golden():
     np.testing.assert_array_equal(drl.random.randint(K(6), (333, 3), 0, 5).cpu().numpy(), g['randint_key6_333x3'])
     np.testing.assert_array_equal(drl.random.randint(K(6), (333, 3), 0, 5, first=100, count=50).cpu().numpy(),
                                   g['randint_key6_333x3'].ravel()[100:150])
+
+
+# ---- top_k ties: frozen step keys whose respawn noise ties among the deciding ranks ---------------------------
+def _tie_cases():
+    import json
+    d = json.load(open(os.path.join(GOLD, 'tie_keys.json')))
+    return [(name, c) for name, c in d.items()]
+
+
+def _load_find_tie_keys():
+    spec = importlib.util.spec_from_file_location('find_tie_keys', os.path.join(GOLD, 'find_tie_keys.py'))
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    return m
+
+
+@pytest.mark.parametrize('name,case', _tie_cases())
+def test_top_k_tie_goes_to_the_lower_index_on_both_oracles(c_oracle, name, case):
+    """tests/golden/tie_keys.json (made by find_tie_keys.py): step keys whose spawn_air noise carries the SAME mantissa
+    on two candidates among the first J + 1 ranks.  The oracle must hand the ranks out by (noise descending, cell
+    index ascending) -- jax.lax.top_k's tie rule -- rank i to drone i (env.py:76-85); here that order is
+    recomputed from the raw bits, independently of the oracle's own top_k, and both oracles must match it."""
+    from oracle import jaxrand as jr
+    F = _load_find_tie_keys()
+    C = c_oracle
+    cfg = case['params']
+    p, s0, acts, cand, J = F.air_setup(cfg, case['reset_seed'], case['action_seed'])
+    assert J == case['J'] and len(case['step_keys']) >= 1
+    G = p.grid_size
+    for kk in case['step_keys']:
+        key = np.array(kk, dtype=np.uint32)
+        m = F.air_mantissas(key[None, :], G * G)[0]
+        m[~cand] = -1
+        order = np.lexsort((np.arange(G * G), -m))            # noise descending, then cell index ascending
+        top = m[order[:J + 1]]
+        assert (top[1:] == top[:-1]).any() and top[-1] >= 0, 'the frozen key no longer ties among the deciding ranks'
+        s1, rew, dones = E.step(key, s0.copy(), acts, p)
+        dones = np.asarray(dones)
+        for i in np.nonzero(dones)[0]:
+            pos = int(order[i])
+            assert (int(s1.air_x[i]), int(s1.air_y[i])) == (pos // G, pos % G), f'{name}: drone {i} did not take rank {i}'
+        # the threaded C oracle agrees with the NumPy restatement on the same step
+        keys1 = key[None, :].copy()
+        bs = C.reset(jr.PRNGKey(case['reset_seed'])[None, :].copy(), p)
+        crew, cdone = C.step(keys1, bs, acts[None, :].copy(), p)
+        assert np.array_equal(bs.ground[0], s1.ground) and np.array_equal(bs.air_x[0], s1.air_x)
+        assert np.array_equal(bs.air_y[0], s1.air_y) and np.array_equal(cdone[0], dones)
+        assert np.array_equal(bits(crew[0]), bits(rew))

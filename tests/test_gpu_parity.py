@@ -114,6 +114,47 @@ def test_scatter_aliasing_stress_matches_oracle(c_oracle, G, n, r, extra):
                                           err_msg=f'obs step {t}')
 
 
+def _tie_cases():
+    import json
+    import os
+    d = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden', 'tie_keys.json')))
+    return list(d.items())
+
+
+@pytest.mark.parametrize('name,case', _tie_cases())
+def test_top_k_ties_match_oracle(c_oracle, name, case):
+    """Step keys whose spawn_air noise ties among the deciding ranks (tests/golden/tie_keys.json; the CPU suite checks
+    that the tie is there and that the oracle resolves it by the lower cell index): the warp kernel's packed rank keys
+    and the CTA-mode fast kernel's counted ranks must resolve it the same way.  64 envs with the same state and
+    actions, the tie keys planted among ordinary keys."""
+    import dronerl_b200 as drl
+    C = c_oracle
+    N = 64
+    p = drl.DroneEnvParams(**case['params'])
+    op = oracle_params(p)
+    n = p.n_drones
+    env = drl.DeliveryDrones()
+    reset_keys = np.repeat(drl.random.PRNGKey(case['reset_seed'])[None, :], N, axis=0).astype(np.uint32)
+    acts1 = np.random.default_rng(case['action_seed']).integers(0, 5, size=n).astype(np.int32)
+    acts = np.repeat(acts1[None, :], N, axis=0)
+    keys = C.split(drl.random.PRNGKey(4242), N)
+    planted = {}
+    for i, kk in enumerate(case['step_keys']):
+        for e in (3 + 17 * i, 40 + 5 * i):
+            keys[e] = np.array(kk, dtype=np.uint32)
+            planted[e] = kk
+    state = env.reset(torch.from_numpy(reset_keys).cuda(), p)
+    ostate = C.reset(reset_keys, op)
+    assert_state_equal(state, ostate, 'after reset')
+    out = env.step(torch.from_numpy(keys).cuda(), state, torch.from_numpy(acts).cuda(), p, return_obs=True)
+    orew, odone = C.step(keys, ostate, acts, op)
+    assert odone[list(planted)].any()
+    assert_state_equal(out[0], ostate, f'{name}: step with tie keys at envs {sorted(planted)}')
+    np.testing.assert_array_equal(out[2].cpu().numpy(), odone)
+    np.testing.assert_array_equal(out[1].cpu().numpy().view(np.uint32), orew.view(np.uint32))
+    np.testing.assert_array_equal(out[3].cpu().numpy().view(np.uint32), C.get_obs(ostate, op).view(np.uint32))
+
+
 def test_parent_key_split_matches_explicit_keys(c_oracle):
     """step(key(2,), ...) on a batched state == vmap(step)(split(key, N), ...)  (train_jax.py:52-54)."""
     import dronerl_b200 as drl
