@@ -47,6 +47,7 @@ SYMBOLS = {
     'drl_step_keyed': (ctypes.c_int, [_vp, c_u32p, c_u32p, _i32, _vp, _vp, _vp, _vp, _vp]),
     'drl_get_obs': (ctypes.c_int, [_vp, _vp, _vp]),
     'drl_step_host': (ctypes.c_int, [_vp, c_u32p, _vp, _vp, _vp, _vp, _vp, _vp]),
+    'drl_host_timing': (ctypes.c_int, [_vp, ctypes.POINTER(ctypes.c_double), _i32]),
     'drl_rollout_random': (ctypes.c_int, [_vp, c_u32p, _i32, _i32, _i64, _vp, _vp, _vp, _vp, _vp, _vp]),
     'drl_stats_read': (ctypes.c_int, [_vp, ctypes.POINTER(ctypes.c_uint64), _vp]),
     'drl_stats_clear': (ctypes.c_int, [_vp, _vp]),

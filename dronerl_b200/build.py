@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC_DIR = os.path.join(HERE, 'csrc')
 SOURCES = ['dronerl_b200.cu']
-HEADERS = ['env_kernels.cuh', 'threefry.cuh', os.path.join('..', '..', 'include', 'dronerl_b200.h')]
+HEADERS = sorted(f for f in os.listdir(SRC_DIR) if f.endswith(('.cuh', '.h'))) + [os.path.join('..', '..', 'include', 'dronerl_b200.h')]
 LIB_PATH = os.environ.get('DRONERL_B200_LIB') or os.path.join(HERE, 'libdronerl_b200.so')   # override: A/B kernel experiments
 
 NVCC_FLAGS = [

@@ -6,6 +6,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <time.h>
 
 #include <new>
 
@@ -15,6 +16,9 @@
 
 using namespace drl;
 
+#ifndef DRL_HOST_AUTO_MAPPED
+#define DRL_HOST_AUTO_MAPPED 0   // drl_step_host with DRL_HOST_PIPE unset: prefer the zero-copy pipeline when the buffers allow it
+#endif
 #ifndef DRL_QMAX
 #define DRL_QMAX 8       // envs per warp for n_drones <= 4 (4 or 8)
 #endif
@@ -415,6 +419,36 @@ __global__ void k_randint(uint32_t a0, uint32_t a1, uint32_t b0, uint32_t b1, co
     if (bb.in1) out[bb.f1 - first] = (int8_t)(((hi1 % span) * mult + (lo1 % span)) % span);
 }
 
+// Both derivations of one random-agent rollout step in ONE launch (train_jax.py:43-44 and :52-53): threads
+// [0, nb_a) hash one block of randint's two draws each (two int8 actions), threads [nb_a, nb_a + nb_k) one block of
+// split(key, Ng) (two key words).  Same arithmetic as k_randint / k_split_keys; one launch and one launch gap fewer
+// per step, which is what a step costs extra once the slice is small (strong scaling: 131,072 envs per GPU).
+struct DeriveArgs {
+    uint32_t a0, a1, b0, b1;          // k1, k2 = split(action key) of _randint
+    uint32_t k0, k1;                  // parent of the per-env keys
+    uint32_t span, mult;
+    long long total, first, count, bmin_a, nb_a;     // actions: flat randint vector, local element range, block range
+    long long Ng, off, Nl, bmin_k, nb_k;             // keys: global envs, local row range, block range
+};
+__global__ void __launch_bounds__(256)
+k_derive(const __grid_constant__ DeriveArgs d, int8_t* __restrict__ acts, uint32_t* __restrict__ keys) {
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < d.nb_a) {
+        const BitsBlock bb = bits_block(d.bmin_a + t, d.total, d.first, d.count);
+        uint32_t hi0, hi1, lo0, lo1;
+        drl_threefry2x32(d.a0, d.a1, (uint32_t)bb.f0, bb.c1, hi0, hi1);
+        drl_threefry2x32(d.b0, d.b1, (uint32_t)bb.f0, bb.c1, lo0, lo1);
+        if (bb.in0) acts[bb.f0 - d.first] = (int8_t)(((hi0 % d.span) * d.mult + (lo0 % d.span)) % d.span);
+        if (bb.in1) acts[bb.f1 - d.first] = (int8_t)(((hi1 % d.span) * d.mult + (lo1 % d.span)) % d.span);
+    } else if (t - d.nb_a < d.nb_k) {
+        const BitsBlock bb = bits_block(d.bmin_k + (t - d.nb_a), 2 * d.Ng, 2 * d.off, 2 * d.Nl);
+        uint32_t o0, o1;
+        drl_threefry2x32(d.k0, d.k1, (uint32_t)bb.f0, bb.c1, o0, o1);
+        if (bb.in0) keys[bb.f0 - 2 * d.off] = o0;
+        if (bb.in1) keys[bb.f1 - 2 * d.off] = o1;
+    }
+}
+
 // out[i] = split(key, num)[i] with the key read from device memory; one block, in-place safe (``out`` may
 // start at ``dkey``): every thread reads the key before anyone writes
 __global__ void k_key_split_dev(const uint32_t* dkey, int num, uint32_t* out) {
@@ -458,8 +492,26 @@ struct drl_env {
     DevCfg fast_dc;       // the fast kernel's shared-memory layout (otherwise equal to dc)
     int* d_redo;          // [64] headers (4 ints per concurrent launch slot) + [N] redo list
     int smem_optin;       // device limit of opt-in dynamic shared memory per CTA
+    // A/B switches, read ONCE from the environment in drl_create (never on the step path)
+    int host_pipe;        // drl_step_host: HOSTPIPE_AUTO / _CHUNKS / _SINGLE / _MAPPED
+    int host_fuse_keys, host_chunks, host_grid_pct, fuse_keys, fuse_actions, split_derive;
+    int test_drop_flag;   // test hook (DRL_TEST_DROP_INPUT_FLAG=k): the next k drl_step_host calls lose one input flag
+    unsigned long long spin_ns;   // bound of the HP kernel's wait for an input flag
+    unsigned* h_pipe_err; // pinned host copy of the pipeline's error word
+    int host_failed;      // the previous drl_step_host call failed: re-arm counters before the next one
+    // one ticketed launch per slot may be in flight: the event of the last launch on each slot orders a launch that
+    // arrives on a DIFFERENT stream behind it (17 slots: 16 step slots + the obs kernel's)
+    cudaEvent_t slot_event[17];
+    cudaStream_t slot_stream[17];
+    unsigned char slot_used[17];
+    int multi_stream;     // the handle has seen ticketed launches on more than one stream
+    // drl_step_host timing (drl_host_timing): host time spent enqueueing vs blocked in the final synchronize
+    double t_enqueue_ms, t_sync_ms;
+    long long t_calls;
+    int last_host_pipe;   // the pipeline the last drl_step_host call actually took
     char err[512];
 };
+enum { HOSTPIPE_AUTO = 0, HOSTPIPE_CHUNKS = 1, HOSTPIPE_SINGLE = 2, HOSTPIPE_MAPPED = 3 };
 
 static char g_create_err[512] = "";
 
@@ -627,6 +679,37 @@ static int configure_launches(drl_env* e) {
     return DRL_OK;
 }
 
+// One ticketed launch per slot may be in flight: launches of a slot share its ticket counters (and, in CTA mode, its
+// redo-list header), which the last worker of a launch re-arms.  On one stream that holds by stream order.  When a
+// launch arrives on a DIFFERENT stream than the slot's previous one it is ordered behind it: the first time a handle
+// sees a second stream the device is synchronised once, from then on every ticketed launch records the slot's event
+// and a launch on another stream waits for it.  Streams under CUDA-graph capture are left alone (nothing executes at
+// capture time; the order of graph replays against other work on the handle is the caller's to keep).
+static int slot_enter(drl_env* env, int slot, cudaStream_t s, bool* track) {
+    *track = false;
+    const bool differs = env->slot_used[slot] && env->slot_stream[slot] != s;
+    if (!differs && !env->multi_stream) { env->slot_stream[slot] = s; env->slot_used[slot] = 1; return DRL_OK; }
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(s, &cs) != cudaSuccess) { (void)cudaGetLastError(); cs = cudaStreamCaptureStatusNone; }
+    if (cs != cudaStreamCaptureStatusNone) return DRL_OK;
+    if (!env->multi_stream) {
+        CUDA_TRY(env, cudaDeviceSynchronize());
+        env->multi_stream = 1;
+    } else if (differs && env->slot_event[slot]) {
+        CUDA_TRY(env, cudaStreamWaitEvent(s, env->slot_event[slot], 0));
+    }
+    *track = true;
+    return DRL_OK;
+}
+static int slot_leave(drl_env* env, int slot, cudaStream_t s, bool track) {
+    if (!track) return DRL_OK;
+    if (!env->slot_event[slot]) CUDA_TRY(env, cudaEventCreateWithFlags(&env->slot_event[slot], cudaEventDisableTiming));
+    CUDA_TRY(env, cudaEventRecord(env->slot_event[slot], s));
+    env->slot_stream[slot] = s;
+    env->slot_used[slot] = 1;
+    return DRL_OK;
+}
+
 // One step of the env range [first, first + count) of the bound state: the warp kernel, or in CTA mode the fast
 // kernel followed by the general kernel on the fast kernel's redo list (``slot`` < 16 names the list header, so
 // launches that overlap on different streams use different ones).  Returns DRL_OK and adds the kernels launched
@@ -654,6 +737,11 @@ static void fill_derivation(const drl_env* env, DevCfg& dc, long long first, con
     }
 }
 
+static int launch_step_inner(drl_env* env, long long first, long long count, const uint32_t* d_keys, const int8_t* d_actions,
+                             float* d_rewards, uint8_t* d_dones, float* d_obs, cudaStream_t s, int slot, int* launches,
+                             const StepKeys* sk, int grid_pct, unsigned* chunk_done, int chunk_shift,
+                             const unsigned* chunk_in, unsigned in_epoch, int in_shift);
+
 static int launch_step(drl_env* env, long long first, long long count, const uint32_t* d_keys, const int8_t* d_actions,
                        float* d_rewards, uint8_t* d_dones, float* d_obs, cudaStream_t s, int slot, int* launches,
                        const StepKeys* sk = nullptr, int grid_pct = 100, unsigned* chunk_done = nullptr, int chunk_shift = 0,
@@ -661,6 +749,21 @@ static int launch_step(drl_env* env, long long first, long long count, const uin
     // grid_pct < 100: launch on that share of the resident CTA count, so that chunk launches on two streams run side
     // by side (with ticketed env order every worker of a launch finishes at the same moment; a full-size grid would
     // leave the next chunk's start-up and this chunk's tail exposed at every boundary)
+    bool track = false;
+    if (!env->static_order) {
+        const int rc = slot_enter(env, slot, s, &track);
+        if (rc) return rc;
+    }
+    const int rc_all = launch_step_inner(env, first, count, d_keys, d_actions, d_rewards, d_dones, d_obs, s, slot, launches, sk,
+                                         grid_pct, chunk_done, chunk_shift, chunk_in, in_epoch, in_shift);
+    if (rc_all) return rc_all;
+    return slot_leave(env, slot, s, track);
+}
+
+static int launch_step_inner(drl_env* env, long long first, long long count, const uint32_t* d_keys, const int8_t* d_actions,
+                             float* d_rewards, uint8_t* d_dones, float* d_obs, cudaStream_t s, int slot, int* launches,
+                             const StepKeys* sk, int grid_pct, unsigned* chunk_done, int chunk_shift,
+                             const unsigned* chunk_in, unsigned in_epoch, int in_shift) {
     DevCfg dc = env->dc;
     dc.N = count;
     dc.chunk_done = chunk_done;
@@ -668,6 +771,8 @@ static int launch_step(drl_env* env, long long first, long long count, const uin
     dc.chunk_in = chunk_in;
     dc.in_epoch = in_epoch;
     dc.in_shift = in_shift;
+    dc.hp_err = env->d_chunk_done ? env->d_chunk_done + 127 : nullptr;
+    dc.spin_ns = env->spin_ns;
     fill_derivation(env, dc, first, sk);
     const long long n = dc.n;
     uint8_t* ground = env->d_ground + first * dc.GS;
@@ -793,6 +898,26 @@ int drl_create(const drl_config* cfg, drl_env** out) {
     c.tile_stride = round_up(c.tile_drones * cell_bytes, 128);
     c.tile_bufs = 1;
     if (const char* tb = getenv("DRL_TILE_BUFS")) c.tile_bufs = (e->warp_mode && tb[0] == '2') ? 2 : 1;   // A/B switch
+    {   // every other A/B switch: read here, once per handle
+        auto flag = [](const char* name) { const char* v = getenv(name); return v && v[0] == '1'; };
+        auto num = [](const char* name, int dflt, int lo, int hi) {
+            const char* v = getenv(name);
+            if (!v) return dflt;
+            const int x = atoi(v);
+            return x < lo ? lo : x > hi ? hi : x;
+        };
+        const char* hp = getenv("DRL_HOST_PIPE");        // chunks | single | mapped (default: auto)
+        e->host_pipe = !hp ? HOSTPIPE_AUTO : hp[0] == 'c' ? HOSTPIPE_CHUNKS : hp[0] == 's' ? HOSTPIPE_SINGLE
+                     : hp[0] == 'm' ? HOSTPIPE_MAPPED : HOSTPIPE_AUTO;
+        e->host_fuse_keys = flag("DRL_HOST_FUSE_KEYS");
+        e->host_chunks = num("DRL_HOST_CHUNKS", 8, 1, 15);
+        e->host_grid_pct = num("DRL_HOST_GRID_PCT", 100, 10, 100);
+        e->fuse_keys = flag("DRL_FUSE_KEYS");
+        e->fuse_actions = flag("DRL_FUSE_ACTIONS");
+        e->split_derive = flag("DRL_SPLIT_DERIVE");      // rollout: separate randint + split launches (round-1 path)
+        e->test_drop_flag = num("DRL_TEST_DROP_INPUT_FLAG", 0, 0, 1000);
+        e->spin_ns = (unsigned long long)num("DRL_HOST_SPIN_TIMEOUT_MS", 2000, 1, 600000) * 1000000ull;
+    }
     e->envs_per_warp = !e->warp_mode ? 1 : n <= 4 ? DRL_QMAX : n <= 8 ? 4 : n <= 16 ? 2 : 1;
     const int Q = e->envs_per_warp;
     c.sel_maxj = c.k_spawn > n ? c.k_spawn : n;
@@ -854,6 +979,9 @@ void drl_destroy(drl_env* env) {
         if (env->pipe_end[i]) cudaEventDestroy(env->pipe_end[i]);
     }
     if (env->pipe_begin) cudaEventDestroy(env->pipe_begin);
+    for (int i = 0; i < 17; ++i)
+        if (env->slot_event[i]) cudaEventDestroy(env->slot_event[i]);
+    if (env->h_pipe_err) cudaFreeHost(env->h_pipe_err);
     delete env;
 }
 
@@ -1025,8 +1153,14 @@ int drl_get_obs(drl_env* env, void* d_obs, void* stream) {
     CUDA_TRY(env, cudaSetDevice(env->cfg.device));
     const int threads = env->warp_mode ? kWarpsPerBlock * 32 : kCtaThreads;
     unsigned* queue = env->static_order ? nullptr : reinterpret_cast<unsigned*>(env->d_stats + DRL_NUM_STATS + 2) + 2 * 16;
-    return launch(env, "obs kernel", (const void*)pick_obs(env), env->grid_obs, threads, env->smem_bytes, stream, env->dc,
-                  (const uint8_t*)env->d_ground, (const uint32_t*)env->d_drones, (float*)d_obs, queue);
+    bool track = false;
+    if (queue != nullptr) {
+        const int rc = slot_enter(env, 16, (cudaStream_t)stream, &track);
+        if (rc) return rc;
+    }
+    const int rc = launch(env, "obs kernel", (const void*)pick_obs(env), env->grid_obs, threads, env->smem_bytes, stream, env->dc,
+                          (const uint8_t*)env->d_ground, (const uint32_t*)env->d_drones, (float*)d_obs, queue);
+    return rc ? rc : slot_leave(env, 16, (cudaStream_t)stream, track);
 }
 
 static int ensure_scratch(drl_env* env) {
@@ -1036,8 +1170,11 @@ static int ensure_scratch(drl_env* env) {
     CUDA_TRY(env, cudaMalloc(&env->s_actions, c.N * c.n));
     CUDA_TRY(env, cudaMalloc(&env->s_rewards, c.N * c.n * 4));
     CUDA_TRY(env, cudaMalloc(&env->s_dones, c.N * c.n));
+    // [0, 64) envs finished per output chunk | [64, 127) input flags | [127] error word of the pipeline
     CUDA_TRY(env, cudaMalloc(&env->d_chunk_done, 128 * sizeof(unsigned)));
     CUDA_TRY(env, cudaMemset(env->d_chunk_done, 0, 128 * sizeof(unsigned)));
+    CUDA_TRY(env, cudaHostAlloc(&env->h_pipe_err, 64, cudaHostAllocDefault));
+    env->h_pipe_err[0] = 0u;
     for (int i = 0; i < 2; ++i) {
         CUDA_TRY(env, cudaStreamCreateWithFlags(&env->pipe_stream[i], cudaStreamNonBlocking));
         CUDA_TRY(env, cudaEventCreateWithFlags(&env->pipe_end[i], cudaEventDisableTiming));
@@ -1064,13 +1201,59 @@ static stream_value32_fn stream_write_value32() {
     return fn;
 }
 
-// drl_step_host, warp mode: ONE ticketed step launch over the whole slice.  The envs are stepped in index order
-// (tickets), every warp reports the envs it has finished to per-chunk counters, and the copy stream waits on those
-// counters (stream memory op) to move each chunk's rewards and dones to the host while later chunks are still being
+static double now_ms() {
+    timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return (double)ts.tv_sec * 1e3 + (double)ts.tv_nsec * 1e-6;
+}
+
+// Final synchronize of a drl_step_host call, with the host-side time split recorded for drl_host_timing.
+static int host_sync(drl_env* env, cudaStream_t s, double t_begin) {
+    const double t_enq = now_ms();
+    const cudaError_t ce = cudaStreamSynchronize(s);
+    const double t_end = now_ms();
+    env->t_enqueue_ms += t_enq - t_begin;
+    env->t_sync_ms += t_end - t_enq;
+    env->t_calls += 1;
+    if (ce != cudaSuccess) {
+        env->host_failed = 1;
+        return fail(env, DRL_ECUDA, "drl_step_host: cudaStreamSynchronize failed: CUDA error %s%lld", "", (long long)ce);
+    }
+    return DRL_OK;
+}
+
+// Device-side alias of a page-locked, mapped host pointer (nullptr: pageable or unmapped memory).
+static void* mapped_alias(const void* h) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, h) != cudaSuccess) { (void)cudaGetLastError(); return nullptr; }
+    if (at.type != cudaMemoryTypeHost || at.devicePointer == nullptr) return nullptr;
+    return at.devicePointer;
+}
+
+// drl_step_host, zero-copy form: when the three host buffers are page-locked and mapped (cudaHostAlloc /
+// cudaHostRegister; torch's pin_memory()), the ordinary step kernel reads the actions from and writes rewards and dones
+// to HOST memory directly over PCIe -- a group of 8 envs reads 32 B of actions (prefetched one group ahead, so the
+// round trip is hidden) and leaves 128 B of rewards and 32 B of dones as coalesced posted writes.  No staging
+// buffers, no copy-engine calls, no flags: the call is key split + one launch + synchronize (3 driver calls against
+// ~75 of the copy-engine pipeline), which is what matters when eight processes share one host.
+static int step_host_mapped(drl_env* env, const uint32_t key[2], const int8_t* d_act, float* d_rew, uint8_t* d_don, void* d_obs,
+                            cudaStream_t s, double t_begin) {
+    int rc = env->host_fuse_keys ? DRL_OK : drl_split_keys(env, key, env->s_keys, s);
+    if (rc) return rc;
+    const StepKeys sk = {key, nullptr, 0};
+    rc = launch_step(env, 0, env->dc.N, env->host_fuse_keys ? nullptr : env->s_keys, d_act, d_rew, d_don, (float*)d_obs, s, 0,
+                     nullptr, env->host_fuse_keys ? &sk : nullptr);
+    if (rc) return rc;
+    return host_sync(env, s, t_begin);
+}
+
+// drl_step_host, warp mode, copy-engine form: ONE ticketed step launch over the whole slice.  The envs are stepped in
+// index order (tickets), every warp reports the envs it has finished to per-chunk counters, and the copy stream waits on
+// those counters (stream memory op) to move each chunk's rewards and dones to the host while later chunks are still being
 // stepped.  Compared with one launch per chunk this has no kernel boundaries: no start-up, tail and quantisation loss
 // per chunk (with tickets all workers of a launch finish together, so consecutive chunk launches no longer overlap).
 static int step_host_single(drl_env* env, const uint32_t key[2], const int8_t* h_actions, float* h_rewards, uint8_t* h_dones,
-                            void* d_obs, cudaStream_t s, stream_value32_fn wait32) {
+                            void* d_obs, cudaStream_t s, stream_value32_fn wait32, double t_begin) {
     const DevCfg& c = env->dc;
     const long long n = c.n;
     int shift = 15;                                           // output chunks of 2^shift envs, at most 17 of them
@@ -1081,37 +1264,47 @@ static int step_host_single(drl_env* env, const uint32_t key[2], const int8_t* h
     cudaStream_t ps = env->pipe_stream[0], pin = env->pipe_stream[1];
     stream_value32_fn write32 = stream_write_value32();
     unsigned* const flags_in = env->d_chunk_done + 64;
+    unsigned* const d_err = env->d_chunk_done + 127;
     const unsigned epoch = ++env->host_epoch;
     int rc = drl_split_keys(env, key, env->s_keys, s);       // split(key, N), train_jax.py:53
     if (rc) return rc;
+    // counters, flags-independent state of the pipeline: output counters and the error word start at zero; after a
+    // failed call the ticket counters of slot 0 are re-armed too (a launch that was torn down leaves them dirty)
     CUDA_TRY(env, cudaMemsetAsync(env->d_chunk_done, 0, 64 * sizeof(unsigned), s));
+    CUDA_TRY(env, cudaMemsetAsync(d_err, 0, sizeof(unsigned), s));
+    if (env->host_failed) {
+        CUDA_TRY(env, cudaMemsetAsync(reinterpret_cast<unsigned*>(env->d_stats + DRL_NUM_STATS + 2), 0, 2 * sizeof(unsigned), s));
+        env->host_failed = 0;
+    }
+    env->h_pipe_err[0] = 0u;
     if (write32 == nullptr) CUDA_TRY(env, cudaMemcpyAsync(env->s_actions, h_actions, c.N * n, cudaMemcpyHostToDevice, s));
     CUDA_TRY(env, cudaEventRecord(env->pipe_begin, s));     // the copy streams start behind the caller's earlier work
-    // The step launch goes first: its warps wait (only at the very beginning -- the copies run far ahead of the
-    // stepping) for the flag of the input chunk they are about to read, so the GPU is already stepping chunk 0 while
-    // the host is still enqueueing the other copies.
-    rc = launch_step(env, 0, c.N, env->s_keys, env->s_actions, env->s_rewards, env->s_dones, (float*)d_obs, s, 0, nullptr,
-                     nullptr, 100, env->d_chunk_done, shift, write32 != nullptr ? flags_in : nullptr, epoch, in_shift);
-    if (rc) return rc;
-    // From here on a failed enqueue must not leave the launch waiting for flags that will never be written.
-    auto bail = [&](const char* what) {
-        if (write32 != nullptr)
-            for (int k = 0; k < chunks_in; ++k) (void)write32((CUstream)pin, (CUdeviceptr)(uintptr_t)(flags_in + k), epoch, 0u);
-        (void)cudaGetLastError();
-        return fail(env, DRL_ECUDA, "drl_step_host: %s failed", what);
-    };
+    // Input side FIRST: the chunked H2D copies and their flag writes are enqueued on ``pin`` before the launch, so the
+    // launch never depends on host work that follows it (a serialising tool -- CUDA_LAUNCH_BLOCKING, compute-sanitizer,
+    // a profiler's kernel replay -- would otherwise wait for flags that are never enqueued).  The overlap is the same:
+    // ``pin`` depends only on pipe_begin, the kernel's warps wait per chunk for the flag of the chunk they read.
+    const int drop = env->test_drop_flag > 0 ? chunks_in - 1 : -1;   // test hook: this call loses its last input flag
+    if (env->test_drop_flag > 0) --env->test_drop_flag;
     if (write32 != nullptr) {
-        if (cudaStreamWaitEvent(pin, env->pipe_begin, 0) != cudaSuccess) return bail("cudaStreamWaitEvent");
+        CUDA_TRY(env, cudaStreamWaitEvent(pin, env->pipe_begin, 0));
         for (int k = 0; k < chunks_in; ++k) {
             const long long first = (long long)k << in_shift;
             const long long count = c.N - first < per_in ? c.N - first : per_in;
-            if (cudaMemcpyAsync(env->s_actions + first * n, h_actions + first * n, count * n, cudaMemcpyHostToDevice, pin) != cudaSuccess)
-                return bail("cudaMemcpyAsync of the actions");
+            CUDA_TRY(env, cudaMemcpyAsync(env->s_actions + first * n, h_actions + first * n, count * n, cudaMemcpyHostToDevice, pin));
+            if (k == drop) continue;
             if (write32((CUstream)pin, (CUdeviceptr)(uintptr_t)(flags_in + k), (cuuint32_t)epoch, CU_STREAM_WRITE_VALUE_DEFAULT) !=
-                CUDA_SUCCESS)
-                return bail("cuStreamWriteValue32");
+                CUDA_SUCCESS) {
+                // a flag that cannot be enqueued: finish this call on the per-chunk path instead (nothing launched yet)
+                (void)cudaStreamSynchronize(pin);
+                return fail(env, DRL_ECUDA, "drl_step_host: cuStreamWriteValue32 failed%s");
+            }
         }
     }
+    rc = launch_step(env, 0, c.N, env->s_keys, env->s_actions, env->s_rewards, env->s_dones, (float*)d_obs, s, 0, nullptr,
+                     nullptr, 100, env->d_chunk_done, shift, write32 != nullptr ? flags_in : nullptr, epoch, in_shift);
+    if (rc) return rc;
+    // From here on a failed enqueue leaves the launch running; the kernel's bounded wait and the error word cover it.
+    env->host_failed = 1;
     CUDA_TRY(env, cudaStreamWaitEvent(ps, env->pipe_begin, 0));
     for (int k = 0; k < chunks; ++k) {
         const long long first = (long long)k << shift;
@@ -1124,7 +1317,16 @@ static int step_host_single(drl_env* env, const uint32_t key[2], const int8_t* h
     }
     CUDA_TRY(env, cudaEventRecord(env->pipe_end[0], ps));
     CUDA_TRY(env, cudaStreamWaitEvent(s, env->pipe_end[0], 0));
-    CUDA_TRY(env, cudaStreamSynchronize(s));
+    // the error word travels behind the kernel itself (stream s), not behind the copies
+    CUDA_TRY(env, cudaMemcpyAsync(env->h_pipe_err, d_err, sizeof(unsigned), cudaMemcpyDeviceToHost, s));
+    rc = host_sync(env, s, t_begin);
+    if (rc) return rc;
+    if (env->h_pipe_err[0] != 0u) {
+        (void)cudaStreamSynchronize(pin);
+        return fail(env, DRL_ECUDA, "drl_step_host: an input chunk did not arrive within %s%lld ms; the launch was abandoned and "
+                    "the env state is undefined (reset before stepping again)", "", (long long)(env->spin_ns / 1000000ull));
+    }
+    env->host_failed = 0;
     return DRL_OK;
 }
 
@@ -1134,24 +1336,41 @@ int drl_step_host(drl_env* env, const uint32_t key[2], const int8_t* h_actions, 
     if (!env->d_ground) return fail(env, DRL_ESTATE, "drl_step_host: state not bound (call drl_bind_state)%s");
     if (h_obs && !d_obs) return fail(env, DRL_EINVAL, "drl_step_host: h_obs needs a device obs buffer too%s");
     if ((uintptr_t)d_obs & 7) return fail(env, DRL_EINVAL, "drl_step_host: obs must be 8-byte aligned%s");
+    const double t_begin = now_ms();
     CUDA_TRY(env, cudaSetDevice(env->cfg.device));
     int rc = ensure_scratch(env);
     if (rc) return rc;
     const DevCfg& c = env->dc;
     const long long n = c.n;
     cudaStream_t s = (cudaStream_t)stream;
-    {
-        const char* hp = getenv("DRL_HOST_PIPE");          // A/B switch: "chunks" = one step launch per chunk
-        const bool want_chunks = hp && hp[0] == 'c';
-        stream_value32_fn wait32 = stream_wait_value32();
-        if (pick_step_hostpipe(env) != nullptr && !env->static_order && !h_obs && !want_chunks && wait32 != nullptr)
-            return step_host_single(env, key, h_actions, h_rewards, h_dones, d_obs, s, wait32);
+    // Which pipeline (DRL_HOST_PIPE, read in drl_create; default auto):
+    //   mapped  zero-copy through mapped pinned host buffers -- any shape; needs page-locked mapped buffers, no h_obs
+    //   single  one ticketed launch + copy engines gated by stream memory ops -- static warp-mode shapes
+    //   chunks  one launch per chunk on two side streams -- everything else
+    const int want = env->host_pipe;
+    if (!h_obs && (want == HOSTPIPE_MAPPED || (want == HOSTPIPE_AUTO && DRL_HOST_AUTO_MAPPED))) {
+        void* da = mapped_alias(h_actions);
+        void* dr = da ? mapped_alias(h_rewards) : nullptr;
+        void* dd = dr ? mapped_alias(h_dones) : nullptr;
+        if (dd != nullptr && !((uintptr_t)dr & 3)) {
+            env->last_host_pipe = HOSTPIPE_MAPPED;
+            return step_host_mapped(env, key, (const int8_t*)da, (float*)dr, (uint8_t*)dd, d_obs, s, t_begin);
+        }
+        if (want == HOSTPIPE_MAPPED)
+            return fail(env, DRL_EINVAL, "drl_step_host: DRL_HOST_PIPE=mapped needs page-locked, mapped host buffers%s");
     }
+    {
+        stream_value32_fn wait32 = stream_wait_value32();
+        if (pick_step_hostpipe(env) != nullptr && !env->static_order && !h_obs && want != HOSTPIPE_CHUNKS && wait32 != nullptr) {
+            env->last_host_pipe = HOSTPIPE_SINGLE;
+            return step_host_single(env, key, h_actions, h_rewards, h_dones, d_obs, s, wait32, t_begin);
+        }
+    }
+    env->last_host_pipe = HOSTPIPE_CHUNKS;
     // split(key, N) (train_jax.py:53): one 11-us kernel into handle-owned scratch ahead of the pipeline.  (Hashing the
     // keys inside the step kernels -- drl_step_keyed -- saves the 8 bytes per env but costs ~50 us per 1M envs there:
     // the extra code pushes the step loop further out of the instruction cache; DRL_HOST_FUSE_KEYS=1 switches back.)
-    const char* fk = getenv("DRL_HOST_FUSE_KEYS");
-    const bool fuse_keys = fk && fk[0] == '1';
+    const bool fuse_keys = env->host_fuse_keys;
     const StepKeys sk = {key, nullptr, 0};
     if (!fuse_keys) {
         rc = drl_split_keys(env, key, env->s_keys, stream);
@@ -1160,14 +1379,12 @@ int drl_step_host(drl_env* env, const uint32_t key[2], const int8_t* h_actions, 
     CUDA_TRY(env, cudaEventRecord(env->pipe_begin, s));
     // chunks of a whole number of 1024-env blocks: H2D actions -> step+obs -> D2H rewards, dones (, obs)
     const long long kMinChunk = 32768;
-    int max_chunks = 8;
-    if (const char* hc = getenv("DRL_HOST_CHUNKS")) max_chunks = atoi(hc) < 1 ? 1 : atoi(hc) > 15 ? 15 : atoi(hc);   // A/B switch
+    const int max_chunks = env->host_chunks;
     int chunks = (int)(c.N / kMinChunk);
     chunks = chunks < 1 ? 1 : chunks > max_chunks ? max_chunks : chunks;
     const long long per = ((c.N + chunks - 1) / chunks + 1023) / 1024 * 1024;
     const long long obs_env = (long long)c.obs_n * c.W2 * 6;     // floats per env
-    int grid_pct = 100;          // smaller grids (two chunk launches side by side) measured slower: 3.1e9 at 50 % vs 3.4e9
-    if (const char* gp = getenv("DRL_HOST_GRID_PCT")) grid_pct = atoi(gp) < 10 ? 10 : atoi(gp) > 100 ? 100 : atoi(gp);   // A/B switch
+    const int grid_pct = env->host_grid_pct;   // smaller grids (two chunk launches side by side) measured slower: 3.1e9 at 50 % vs 3.4e9
     int used = 0;
     for (long long first = 0; first < c.N; first += per, ++used) {
         const long long count = c.N - first < per ? c.N - first : per;
@@ -1187,22 +1404,52 @@ int drl_step_host(drl_env* env, const uint32_t key[2], const int8_t* h_actions, 
         CUDA_TRY(env, cudaEventRecord(env->pipe_end[i], env->pipe_stream[i]));
         CUDA_TRY(env, cudaStreamWaitEvent(s, env->pipe_end[i], 0));
     }
-    CUDA_TRY(env, cudaStreamSynchronize(s));
+    return host_sync(env, s, t_begin);
+}
+
+int drl_host_timing(drl_env* env, double out[4], int32_t reset) {
+    if (!env || !out) return DRL_EINVAL;
+    out[0] = env->t_enqueue_ms;
+    out[1] = env->t_sync_ms;
+    out[2] = (double)env->t_calls;
+    out[3] = (double)env->last_host_pipe;
+    if (reset) { env->t_enqueue_ms = env->t_sync_ms = 0.0; env->t_calls = 0; }
     return DRL_OK;
+}
+
+// randint actions + per-env keys of one rollout step in one launch (k_derive)
+static int launch_derive(drl_env* env, const uint32_t akey[2], const uint32_t ekey[2], int32_t maxval, void* d_actions,
+                         void* d_keys, void* stream) {
+    const long long n = env->dc.n, Ng = env->cfg.num_envs_global, off = env->cfg.env_offset, Nl = env->dc.N;
+    if (Ng * n >= (1ll << 32)) return fail(env, DRL_EINVAL, "rollout: too many actions (>= 2^32)%s");
+    uint32_t k1[2], k2[2];
+    drl_split2(akey, k1, k2);                                      // _randint: k1, k2 = split(key)
+    DeriveArgs d;
+    d.a0 = k1[0]; d.a1 = k1[1]; d.b0 = k2[0]; d.b1 = k2[1];
+    d.k0 = ekey[0]; d.k1 = ekey[1];
+    d.span = (uint32_t)maxval;
+    d.mult = 65536u % d.span;
+    d.mult = (d.mult * d.mult) % d.span;
+    d.total = Ng * n; d.first = off * n; d.count = Nl * n;
+    bits_block_range(d.total, d.first, d.count, &d.bmin_a, &d.nb_a);
+    d.Ng = Ng; d.off = off; d.Nl = Nl;
+    bits_block_range(2 * Ng, 2 * off, 2 * Nl, &d.bmin_k, &d.nb_k);
+    const long long threads = d.nb_a + d.nb_k;
+    return launch(env, "derivation kernel", (const void*)k_derive, (int)((threads + 255) / 256), 256, 0, stream, d,
+                  (int8_t*)d_actions, (uint32_t*)d_keys);
 }
 
 int drl_rollout_random(drl_env* env, uint32_t rng[2], int32_t steps, int32_t reset_every, int64_t step0, void* d_keys,
                        void* d_actions, void* d_rewards, void* d_dones, void* d_obs, void* stream) {
-    if (!env || !rng || steps < 0 || !d_keys || !d_actions) return DRL_EINVAL;
+    if (!env || !rng || steps < 0 || !d_keys || !d_actions || !d_rewards || !d_dones) return DRL_EINVAL;
+    if (!env->d_ground) return fail(env, DRL_ESTATE, "drl_rollout_random: state not bound (call drl_bind_state)%s");
+    CUDA_TRY(env, cudaSetDevice(env->cfg.device));
     int launches = 0;
-    // A/B switch DRL_FUSE_KEYS=1: hash split(key, N) inside the step kernel instead of the 11-us split kernel.  Measured
+    // A/B switch DRL_FUSE_KEYS=1: hash split(key, N) inside the step kernel instead of the derivation kernel.  Measured
     // slower since the step kernels draw tickets (0.990 vs 0.957 ms per step at 1M envs): the step loop no longer fits the
     // instruction cache (ncu: no_instruction is its top stall) and the hash adds to it.
-    const char* fz = getenv("DRL_FUSE_KEYS");
-    const bool fused = fz && fz[0] == '1' && d_rewards && d_dones && env->d_ground &&
-                       env->cfg.num_envs_global * env->dc.n < (1ll << 32);
-    const char* fa = getenv("DRL_FUSE_ACTIONS");
-    const bool fuse_actions = fused && fa && fa[0] == '1';
+    const bool fused = env->fuse_keys && env->cfg.num_envs_global * env->dc.n < (1ll << 32);
+    const bool fuse_actions = fused && env->fuse_actions;
     for (int32_t t = 0; t < steps; ++t) {
         uint32_t nk[2], sub[2];
         drl_split2(rng, nk, sub);                                  // rng, key = split(rng)   train_jax.py:43
@@ -1225,13 +1472,20 @@ int drl_rollout_random(drl_env* env, uint32_t rng[2], int32_t steps, int32_t res
                              (float*)d_obs, (cudaStream_t)stream, 0, &launches, &sk);
             if (rc) return rc;
         } else {
-            rc = drl_randint_actions(env, akey, 5, d_actions, stream);
+            if (env->split_derive) {                                   // round-1 path: two derivation launches
+                rc = drl_randint_actions(env, akey, 5, d_actions, stream);
+                if (rc) return rc;
+                rc = drl_split_keys(env, sub, d_keys, stream);         // split(key, N)           :53
+                if (rc) return rc;
+                launches += 2;
+            } else {
+                rc = launch_derive(env, akey, sub, 5, d_actions, d_keys, stream);   // :44 and :53 in one launch
+                if (rc) return rc;
+                launches += 1;
+            }
+            rc = launch_step(env, 0, env->dc.N, (const uint32_t*)d_keys, (const int8_t*)d_actions, (float*)d_rewards,
+                             (uint8_t*)d_dones, (float*)d_obs, (cudaStream_t)stream, 0, &launches);   // :54-55
             if (rc) return rc;
-            rc = drl_split_keys(env, sub, d_keys, stream);             // split(key, N)           :53
-            if (rc) return rc;
-            rc = drl_step(env, d_keys, d_actions, d_rewards, d_dones, d_obs, stream);   // :54-55
-            if (rc) return rc;
-            launches += 2 + (pick_fast(env) ? 2 : 1);     // randint, key split, step (fast + general kernel in CTA mode)
         }
         drl_split2(rng, nk, sub);                                  // rng, key = split(rng)   :82 (the trainer's batch key)
         rng[0] = nk[0]; rng[1] = nk[1];

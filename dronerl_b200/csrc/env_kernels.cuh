@@ -77,6 +77,8 @@ struct DevCfg {
     const unsigned* chunk_in;  // nullptr: off
     unsigned in_epoch;
     int in_shift;
+    unsigned* hp_err;          // error word of the pipeline: set when an input flag did not arrive within spin_ns
+    unsigned long long spin_ns;
 };
 
 // keys[e] word w of jax.random.split(parent, Ng)[goff + e]  (train_jax.py:53)

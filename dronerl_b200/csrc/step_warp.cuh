@@ -63,22 +63,36 @@ __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsi
 
     GroupInputs<NV> nxt = {};
     int in_ready = -1;                            // HP: input chunk whose flag this warp has already seen
+    bool aborted = false;                         // HP: an input chunk never arrived (bounded wait below)
     auto prefetch = [&](long long g) {
         const long long e0 = g * Q;
         if (e0 < c.N) {
             const int nq = (int)min((long long)Q, c.N - e0);
             if (HP && c.chunk_in != nullptr && (int)(e0 >> c.in_shift) != in_ready) {   // host pipeline: wait until this
                 in_ready = (int)(e0 >> c.in_shift);                                        // group's input chunk has landed
+                // The wait is BOUNDED: if the flag has not shown up after c.spin_ns (a copy that failed asynchronously, a
+                // caller that tore the stream down) the warp raises the handle's error word and stops taking groups, so
+                // the launch winds down and drl_step_host returns DRL_ECUDA instead of hanging the GPU.
+                int dead = 0;
                 if (lane == 0) {
                     const unsigned* f = c.chunk_in + in_ready;
                     unsigned v;
+                    unsigned long long t0 = 0;
                     for (;;) {
                         asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
                         if ((int)(v - c.in_epoch) >= 0) break;
                         __nanosleep(100);
+                        unsigned long long now;
+                        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+                        if (t0 == 0) t0 = now;
+                        if (now - t0 > c.spin_ns || *reinterpret_cast<volatile unsigned*>(c.hp_err) != 0u) {
+                            atomicExch(c.hp_err, 1u);
+                            dead = 1;
+                            break;
+                        }
                     }
                 }
-                __syncwarp();
+                if (__shfl_sync(FULL, dead, 0)) { aborted = true; return; }
             }
 #pragma unroll
             for (int v = 0; v < NV; ++v)
@@ -86,7 +100,11 @@ __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsi
             if (sub < nq) {
                 if (li < n) {
                     nxt.rec = drones[(e0 + sub) * n + li];
-                    nxt.act = c.act_mode ? derive_action(c, e0 + sub, li) : (int)actions[(e0 + sub) * n + li];
+                    // HP: the copy engine is still writing later chunks of ``actions`` while this launch runs, so the
+                    // read must be a coherent one (L2), never the read-only / non-coherent path of const __restrict__
+                    nxt.act = c.act_mode ? derive_action(c, e0 + sub, li)
+                            : HP         ? (int)__ldcg(const_cast<const int8_t*>(actions) + (e0 + sub) * n + li)
+                                         : (int)actions[(e0 + sub) * n + li];
                 }
                 if (!c.key_mode) {
                     const uint2 kk = *reinterpret_cast<const uint2*>(keys + 2 * (e0 + sub));
@@ -123,7 +141,7 @@ __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsi
     int sig_n = 0;
     auto report = [&]() {
         if (HP && c.chunk_done != nullptr && sig_chunk >= 0) {
-            __threadfence();
+            __threadfence_system();     // the consumer of the counter is another agent (stream memory op + copy engine)
             __syncwarp();
             if (lane == 0) atomicAdd(c.chunk_done + sig_chunk, (unsigned)sig_n);
             sig_chunk = -1;
@@ -132,7 +150,7 @@ __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsi
     long long g = first_group;
     prefetch(g);
     long long gn = ticket(g), gnn = 0;
-    for (; g * Q < c.N; g = gn, gn = gnn) {
+    for (; g * Q < c.N && !(HP && aborted); g = gn, gn = gnn) {
         const long long e0 = g * Q;
         const int nq = (int)min((long long)Q, c.N - e0);
         const GroupInputs<NV> cur = nxt;
@@ -385,6 +403,12 @@ __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsi
         if (atomicAdd(queue + 1, 1u) == (unsigned)(total_warps - 1)) {
             queue[0] = 0u;                                  // every warp has drawn its last ticket by now
             queue[1] = 0u;
+            if (HP && c.chunk_done != nullptr && *reinterpret_cast<volatile unsigned*>(c.hp_err) != 0u) {
+                // aborted launch: release every output chunk so the copy stream (and the host behind it) wakes up;
+                // the host finds the error word set and reports the failure
+                for (int k = 0; k < 64; ++k) atomicExch(c.chunk_done + k, 0x40000000u);
+                __threadfence_system();
+            }
         }
     }
     // episode counters: one atomic per counter per warp

@@ -119,6 +119,26 @@ class DroneEnvState:
         return cls(DroneEnvParams(**d['params']), d['ground_raw'].to(device), d['drones_raw'].to(device), d['batched'],
                    d['env_offset'], d['num_envs_global'])
 
+    # ---- renderer export -------------------------------------------------------------
+    def to_render_arrays(self, actions, rewards, env_index=0):
+        """``convert_jax_state(state, actions, rewards)`` of /root/reference/jax_impl/render_util.py:18-30 for one env:
+        ``(ground, air, carrying_package, charge, rewards, actions)`` as host NumPy arrays, where ``air`` is the
+        ``[G, G]`` object grid holding the drone index at each drone's cell (``None`` elsewhere; with several drones
+        on one cell the highest index shows, as NumPy's ``air[air_y, air_x] = arange(n)`` leaves it) -- what
+        ``common/render.py:175`` ``Renderer.render_frame`` takes."""
+        s = self.to_numpy()
+        pick = (lambda a: a[env_index]) if self.batched else (lambda a: a)
+        ground = np.asarray(pick(s['ground']))
+        air_x, air_y = np.asarray(pick(s['air_x'])), np.asarray(pick(s['air_y']))
+        air = np.zeros_like(ground, dtype=np.object_)
+        air[:] = None
+        air[air_y, air_x] = np.arange(air_x.size)
+
+        def host(a):
+            a = a.detach().cpu().numpy() if isinstance(a, torch.Tensor) else np.asarray(a)
+            return a[env_index] if (self.batched and a.ndim > 1) else a
+        return (ground, air, np.asarray(pick(s['carrying_package'])), np.asarray(pick(s['charge'])), host(rewards), host(actions))
+
     def to_numpy(self):
         """The five reference fields as host NumPy arrays in reference dtypes."""
         return {k: getattr(self, k).cpu().numpy() for k in ('ground', 'air_x', 'air_y', 'carrying_package', 'charge')}

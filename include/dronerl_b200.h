@@ -18,6 +18,10 @@
  *  - no call synchronises the device except the ``*_host`` variants and
  *    ``drl_stats_read``; work is enqueued on the given stream.
  *  - one handle per GPU slice; a handle is not thread-safe, distinct handles are.
+ *  - step / get_obs launches of one handle share per-handle work counters, so only one of
+ *    them may be in flight at a time: on one stream that is stream order; a call on a
+ *    different stream than the handle's previous one is ordered behind it by the library
+ *    (an event wait).  Streams under CUDA-graph capture are not tracked.
  *  - there is NO CPU fallback: on a machine without an sm_100 device
  *    ``drl_create`` fails with DRL_ENODEVICE.
  *
@@ -169,13 +173,30 @@ int drl_get_obs(drl_env* env, void* d_obs, void* stream);
  * launch steps the slice in env order; pageable memory works but serialises). */
 int drl_step_host(drl_env* env, const uint32_t key[2], const int8_t* h_actions, float* h_rewards,
                   uint8_t* h_dones, void* d_obs, float* h_obs, void* stream);
+/* Three pipelines serve drl_step_host (environment variable DRL_HOST_PIPE, read once in drl_create):
+ *   "mapped"  the buffers are page-locked AND mapped (cudaHostAlloc / cudaHostRegister; torch pin_memory()): the step
+ *             kernel reads the actions from and writes rewards / dones to host memory directly over PCIe -- three driver
+ *             calls per step, no staging copies;
+ *   "single"  one step launch over the slice, copy engines gated chunk by chunk through stream memory operations
+ *             (static warp-mode shapes);
+ *   "chunks"  one launch per chunk on two side streams (every other case).
+ * A kernel of the "single" pipeline waits for its input chunks with a BOUND (DRL_HOST_SPIN_TIMEOUT_MS, default 2000):
+ * if a chunk never lands the call returns DRL_ECUDA, the env state is then undefined (reset before stepping again) and
+ * the next call starts from re-armed counters.
+ *
+ * drl_host_timing: host-side time of the drl_step_host calls since the last reset of the counters --
+ * out[0] = ms spent enqueueing (entry to the final synchronize), out[1] = ms blocked in that synchronize,
+ * out[2] = calls, out[3] = pipeline of the last call (1 chunks, 2 single, 3 mapped). */
+int drl_host_timing(drl_env* env, double out[4], int32_t reset);
 
 /* Random-agent rollout driver: per step ``rng,k = split(rng)`` -> randint actions,
  * ``rng,k = split(rng)`` -> per-env keys, step+obs; every ``reset_every`` steps
  * (0 = never) ``vmap(reset)(split(rng, N))`` as train_jax.py:43-55,101-104 does.
  * ``rng`` is updated in place.  Scratch buffers (keys, actions) and outputs are
- * caller-owned device memory.  Returns the number of kernels launched (>= 0) or
- * a negative error. */
+ * caller-owned device memory; after the call they hold the last step's actions,
+ * rewards, dones and observations.  Both derivations of a step (randint, split)
+ * run as ONE launch.  Returns the number of kernels launched (>= 0) or a
+ * negative error. */
 int drl_rollout_random(drl_env* env, uint32_t rng[2], int32_t steps, int32_t reset_every, int64_t step0,
                        void* d_keys, void* d_actions, void* d_rewards, void* d_dones, void* d_obs,
                        void* stream);

@@ -76,6 +76,28 @@ def test_library_sass_is_sm100a_with_tma_bulk_store():
     assert 'MATCH.ANY' in sass and 'REDUX' in sass      # warp match_any collisions, redux rank extraction
 
 
+def test_host_pipeline_instance_reads_actions_coherently():
+    """The HP instances of the warp step kernel (drl_step_host's single-launch pipeline) run while the copy engine is
+    still writing later chunks of the actions: their int8 loads must be coherent ones (LDG...STRONG.GPU), never the
+    read-only / non-coherent path (LDG...CONSTANT) that ``const __restrict__`` gives the ordinary instances."""
+    from dronerl_b200 import build
+    build.build()
+    sass = subprocess.run(['cuobjdump', '-sass', build.LIB_PATH], capture_output=True, text=True).stdout
+    fn, loads = None, {}
+    for line in sass.split('\n'):
+        m = re.search(r'Function : (\S+)', line)
+        if m:
+            fn = m.group(1)
+        elif fn and re.search(r'LDG\.E\.[US]8', line):
+            loads.setdefault(fn, []).append(line)
+    hp = {f: v for f, v in loads.items() if 'k_step_warp' in f and 'ELb1EE' in f}
+    plain = {f: v for f, v in loads.items() if 'k_step_warp' in f and 'ELb0EE' in f}
+    assert hp and plain
+    for f, v in hp.items():
+        assert all('CONSTANT' not in x and 'STRONG' in x for x in v), (f, v)
+    assert any('CONSTANT' in x for v in plain.values() for x in v)      # the check can tell the two apart
+
+
 @pytest.mark.skipif(os.path.exists('/dev/nvidia0'), reason='GPU present: creation succeeds there')
 def test_no_cpu_fallback_without_gpu(lib):
     from dronerl_b200 import _lib
