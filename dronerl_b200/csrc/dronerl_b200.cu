@@ -17,7 +17,8 @@
 using namespace drl;
 
 #ifndef DRL_HOST_AUTO_MAPPED
-#define DRL_HOST_AUTO_MAPPED 0   // drl_step_host with DRL_HOST_PIPE unset: prefer the zero-copy pipeline when the buffers allow it
+#define DRL_HOST_AUTO_MAPPED 1   // drl_step_host with DRL_HOST_PIPE unset: the zero-copy pipeline whenever the buffers allow it
+                                 // (measured at 1M envs, one B200: 0.93 ms per call against 1.19 chunks / 1.36 gated launch)
 #endif
 #ifndef DRL_QMAX
 #define DRL_QMAX 8       // envs per warp for n_drones <= 4 (4 or 8)
