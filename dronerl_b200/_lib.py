@@ -45,6 +45,7 @@ SYMBOLS = {
     'drl_reset': (ctypes.c_int, [_vp, _vp, _vp]),
     'drl_step': (ctypes.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     'drl_step_keyed': (ctypes.c_int, [_vp, c_u32p, c_u32p, _i32, _vp, _vp, _vp, _vp, _vp]),
+    'drl_step_noalloc': (ctypes.c_int, [_vp, c_u32p, _vp, _vp, _vp, _vp, _vp]),
     'drl_get_obs': (ctypes.c_int, [_vp, _vp, _vp]),
     'drl_step_host': (ctypes.c_int, [_vp, c_u32p, _vp, _vp, _vp, _vp, _vp, _vp]),
     'drl_host_timing': (ctypes.c_int, [_vp, ctypes.POINTER(ctypes.c_double), _i32]),

@@ -1506,6 +1506,56 @@ int drl_rollout_random(drl_env* env, uint32_t rng[2], int32_t steps, int32_t res
     return launches;
 }
 
+// ---- allocation-free step (no counterpart in the reference) ----------
+// Scratch for the per-env keys of drl_step_noalloc: a file-scope device array instead of a cudaMalloc'ed buffer, so the
+// call allocates nothing.  Every GPU that loads the library holds these DRL_NOALLOC_MAX_ENVS * 8 bytes (1 MiB) until
+// exit.  In HOST code the name below is only a stand-in for the symbol, never a device address: the address comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+static __device__ __align__(256) uint32_t g_noalloc_keys[2 * DRL_NOALLOC_MAX_ENVS];
+static uint32_t* g_noalloc_keys_addr[64];          // per device ordinal, resolved on first use
+
+static int noalloc_keys_ptr(drl_env* env, uint32_t** out) {
+    const int dev = env->cfg.device;
+    if (dev < 0 || dev >= 64) return fail(env, DRL_EINVAL, "drl_step_noalloc: device ordinal out of range%s");
+    if (g_noalloc_keys_addr[dev] == nullptr) {
+        void* p = nullptr;
+        const cudaError_t ce = cudaGetSymbolAddress(&p, g_noalloc_keys);      // the current device is env's (set by the caller)
+        if (ce != cudaSuccess || p == nullptr) {
+            (void)cudaGetLastError();
+            return fail(env, DRL_ECUDA, "drl_step_noalloc: cudaGetSymbolAddress failed: CUDA error %s%lld", "", (long long)ce);
+        }
+        g_noalloc_keys_addr[dev] = (uint32_t*)p;
+    }
+    *out = g_noalloc_keys_addr[dev];
+    return DRL_OK;
+}
+
+int drl_step_noalloc(drl_env* env, const uint32_t key[2], const void* d_actions, void* d_rewards, void* d_dones, void* d_obs,
+                     void* stream) {
+    if (!env || !key || !d_actions || !d_rewards || !d_dones) return DRL_EINVAL;
+    if (!env->d_ground) return fail(env, DRL_ESTATE, "drl_step_noalloc: state not bound (call drl_bind_state)%s");
+    if ((uintptr_t)d_obs & 7) return fail(env, DRL_EINVAL, "drl_step_noalloc: obs must be 8-byte aligned%s");
+    if (env->dc.N > (long long)DRL_NOALLOC_MAX_ENVS)
+        return fail(env, DRL_EINVAL, "drl_step_noalloc: %s%lld envs in this handle exceed the static scratch of %lld envs "
+                    "(DRL_NOALLOC_MAX_ENVS); use drl_step / drl_step_keyed", "", (long long)env->dc.N, (long long)DRL_NOALLOC_MAX_ENVS);
+    CUDA_TRY(env, cudaSetDevice(env->cfg.device));
+    uint32_t* keys = nullptr;
+    int rc = noalloc_keys_ptr(env, &keys);
+    if (rc) return rc;
+    // keys[e] = split(key, N_global)[env_offset + e] (train_jax.py:52-53) into the static scratch: every word of
+    // [0, 2N) is overwritten, nothing has to start at zero (the array keeps the previous call's keys beyond 2N)
+    long long bmin, nb;
+    bits_block_range(2 * env->cfg.num_envs_global, 2 * env->cfg.env_offset, 2 * env->dc.N, &bmin, &nb);
+    rc = launch(env, "split kernel", (const void*)k_split_keys, (int)((nb + 255) / 256), 256, 0, stream, key[0], key[1],
+                (const uint32_t*)nullptr, (long long)env->cfg.num_envs_global, (long long)env->cfg.env_offset,
+                (long long)env->dc.N, keys, bmin, nb);
+    if (rc) return rc;
+    // the ordinary step kernel(s) on launch slot 15 (its own ticket counters / redo header; buffers owned by the handle
+    // since drl_create).  No slot events, no synchronisation: ordering against other work is the caller's stream order.
+    return launch_step_inner(env, 0, env->dc.N, keys, (const int8_t*)d_actions, (float*)d_rewards, (uint8_t*)d_dones,
+                             (float*)d_obs, (cudaStream_t)stream, 15, nullptr, nullptr, 100, nullptr, 0, nullptr, 0u, 0);
+}
+
 int drl_stats_read(drl_env* env, uint64_t* h_out, void* stream) {
     if (!env || !h_out) return DRL_EINVAL;
     CUDA_TRY(env, cudaSetDevice(env->cfg.device));

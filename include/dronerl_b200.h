@@ -201,6 +201,20 @@ int drl_rollout_random(drl_env* env, uint32_t rng[2], int32_t steps, int32_t res
                        void* d_keys, void* d_actions, void* d_rewards, void* d_dones, void* d_obs,
                        void* stream);
 
+/* NO COUNTERPART IN THE REFERENCE -- added for callers that cannot allocate
+ * (code under CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * Same result as drl_split_keys(key) into a scratch buffer followed by drl_step (== drl_step_keyed with d_actions):
+ * the per-env keys split(key, num_envs_global)[env_offset + e] go into a STATIC device array inside the library
+ * (DRL_NOALLOC_MAX_ENVS * 8 bytes = 1 MiB, held by every GPU that loads the library until exit) and the ordinary step
+ * kernel reads them from there.  The call performs no cudaMalloc / cudaFree / allocating library call.
+ *  - handles with num_envs > DRL_NOALLOC_MAX_ENVS are rejected with DRL_EINVAL and a message;
+ *  - ALL calls (all handles on one GPU) share the one array: calls that overlap on the GPU race -- keep them in
+ *    stream order; the array keeps the last call's keys, nothing in it needs clearing between calls;
+ *  - the first call on each device resolves the array's address (cudaGetSymbolAddress): make it outside any capture. */
+#define DRL_NOALLOC_MAX_ENVS 131072
+int drl_step_noalloc(drl_env* env, const uint32_t key[2], const void* d_actions, void* d_rewards, void* d_dones,
+                     void* d_obs, void* stream);
+
 /* Episode statistics (DRL_NUM_STATS uint64 counters); read synchronises ``stream``. */
 int drl_stats_read(drl_env* env, uint64_t* h_out, void* stream);
 int drl_stats_clear(drl_env* env, void* stream);
