@@ -51,7 +51,15 @@ __device__ __forceinline__ void zero_code(const DevCfg& c, const Smem& sm, int t
 
 // ---- warp-per-env kernels (grids up to 128 cells) ---------------------------------------------
 
-template <int NB, int Q, class D, bool HP = false>
+#ifndef DRL_CTA_TURNS
+#define DRL_CTA_TURNS 0      // warp-mode step kernel, A/B: 1 = CTA-level turns with interleaved tile stores (step_warp.cuh).
+                             // Bit-exact but SLOWER in the real kernel: 0.961 vs 0.867 ms at G9/n4, 0.799 vs 0.701 at G8/n3
+                             // (the micro-benchmark's 3 % gain assumes warps of equal work; here every warp waits for the
+                             // CTA's slowest one each turn).  Default: per-warp tickets.
+#endif
+constexpr bool kCT = DRL_CTA_TURNS != 0;
+
+template <int NB, int Q, class D, bool HP = false, bool CT = false>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32, DRL_STEP_MIN_BLOCKS)
 k_step_warp(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint32_t* __restrict__ drones,
             const uint32_t* __restrict__ keys, const int8_t* __restrict__ actions, float* __restrict__ rewards,
@@ -60,9 +68,9 @@ k_step_warp(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5;
     const D d{c};
-    step_warp_body<NB, Q, D, HP>(c, d, smem_raw + (size_t)warp * c.group_bytes, ground, drones, keys, actions, rewards, dones,
-                             obs, stats, (long long)blockIdx.x * kWarpsPerBlock + warp,
-                             (long long)gridDim.x * kWarpsPerBlock, queue);
+    step_warp_body<NB, Q, D, HP, CT>(c, d, smem_raw + (size_t)warp * c.group_bytes, ground, drones, keys, actions, rewards, dones,
+                                     obs, stats, (long long)blockIdx.x * kWarpsPerBlock + warp,
+                                     (long long)gridDim.x * kWarpsPerBlock, queue, smem_raw);
 }
 
 template <int NB>
@@ -431,22 +439,74 @@ struct DeriveArgs {
     long long total, first, count, bmin_a, nb_a;     // actions: flat randint vector, local element range, block range
     long long Ng, off, Nl, bmin_k, nb_k;             // keys: global envs, local row range, block range
 };
+// Every thread owns SEVERAL consecutive blocks -- 4 action blocks (8 hash chains: two draws each) or 2 key blocks -- so
+// the 60-instruction dependent chains of one hash overlap (one block per thread left the kernel latency-bound: 29 us
+// per 1M envs against ~10 us of issue time) and, when the local range starts on a block boundary (always on one GPU),
+// the four int8 actions of a word leave as one 32-bit store and the two key words as one 64-bit store.
+constexpr int kDeriveA = 4, kDeriveK = 2;
 __global__ void __launch_bounds__(256)
 k_derive(const __grid_constant__ DeriveArgs d, int8_t* __restrict__ acts, uint32_t* __restrict__ keys) {
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (t < d.nb_a) {
-        const BitsBlock bb = bits_block(d.bmin_a + t, d.total, d.first, d.count);
-        uint32_t hi0, hi1, lo0, lo1;
-        drl_threefry2x32(d.a0, d.a1, (uint32_t)bb.f0, bb.c1, hi0, hi1);
-        drl_threefry2x32(d.b0, d.b1, (uint32_t)bb.f0, bb.c1, lo0, lo1);
-        if (bb.in0) acts[bb.f0 - d.first] = (int8_t)(((hi0 % d.span) * d.mult + (lo0 % d.span)) % d.span);
-        if (bb.in1) acts[bb.f1 - d.first] = (int8_t)(((hi1 % d.span) * d.mult + (lo1 % d.span)) % d.span);
-    } else if (t - d.nb_a < d.nb_k) {
-        const BitsBlock bb = bits_block(d.bmin_k + (t - d.nb_a), 2 * d.Ng, 2 * d.off, 2 * d.Nl);
-        uint32_t o0, o1;
-        drl_threefry2x32(d.k0, d.k1, (uint32_t)bb.f0, bb.c1, o0, o1);
-        if (bb.in0) keys[bb.f0 - 2 * d.off] = o0;
-        if (bb.in1) keys[bb.f1 - 2 * d.off] = o1;
+    const long long ta = (d.nb_a + kDeriveA - 1) / kDeriveA, tk = (d.nb_k + kDeriveK - 1) / kDeriveK;
+    if (t < ta) {
+        const long long b0 = d.bmin_a + t * kDeriveA;
+        const long long half = (d.total + 1) >> 1;
+        uint32_t h0[kDeriveA], h1[kDeriveA], l0[kDeriveA], l1[kDeriveA];
+#pragma unroll
+        for (int i = 0; i < kDeriveA; ++i) {
+            const long long f1 = half + b0 + i;
+            h0[i] = l0[i] = (uint32_t)(b0 + i);
+            h1[i] = l1[i] = f1 < d.total ? (uint32_t)f1 : 0u;          // odd sizes: the pad counter is zero
+        }
+        drl_threefry2x32_n<kDeriveA>(d.a0, d.a1, h0, h1);
+        drl_threefry2x32_n<kDeriveA>(d.b0, d.b1, l0, l1);
+        uint32_t w0 = 0, w1 = 0;
+#pragma unroll
+        for (int i = 0; i < kDeriveA; ++i) {
+            w0 |= ((((h0[i] % d.span) * d.mult + (l0[i] % d.span)) % d.span) & 0xFFu) << (8 * i);
+            w1 |= ((((h1[i] % d.span) * d.mult + (l1[i] % d.span)) % d.span) & 0xFFu) << (8 * i);
+        }
+        // element f of the flat vector -> acts[f - first]; word-0 elements are b0 .. b0+3, word-1 elements half + b0 ..
+        const long long o0 = b0 - d.first, o1 = half + b0 - d.first, end = d.count;
+        const bool full = b0 + kDeriveA <= d.bmin_a + d.nb_a && b0 + kDeriveA <= half;
+        if (full && o0 >= 0 && o0 + kDeriveA <= end && (((uintptr_t)(acts + o0) & 3) == 0)) *reinterpret_cast<uint32_t*>(acts + o0) = w0;
+        else {
+#pragma unroll
+            for (int i = 0; i < kDeriveA; ++i)
+                if (b0 + i < half && o0 + i >= 0 && o0 + i < end) acts[o0 + i] = (int8_t)((w0 >> (8 * i)) & 0xFFu);
+        }
+        if (full && o1 >= 0 && o1 + kDeriveA <= end && half + b0 + kDeriveA <= d.total && (((uintptr_t)(acts + o1) & 3) == 0))
+            *reinterpret_cast<uint32_t*>(acts + o1) = w1;
+        else {
+#pragma unroll
+            for (int i = 0; i < kDeriveA; ++i)
+                if (b0 + i < half && half + b0 + i < d.total && o1 + i >= 0 && o1 + i < end) acts[o1 + i] = (int8_t)((w1 >> (8 * i)) & 0xFFu);
+        }
+    } else if (t - ta < tk) {
+        const long long b0 = d.bmin_k + (t - ta) * kDeriveK;
+        const long long size = 2 * d.Ng, half = d.Ng, first = 2 * d.off, end = 2 * d.Nl;     // size is even: no pad counter
+        uint32_t x0[kDeriveK], x1[kDeriveK];
+#pragma unroll
+        for (int i = 0; i < kDeriveK; ++i) {
+            x0[i] = (uint32_t)(b0 + i);
+            x1[i] = (uint32_t)(half + b0 + i);
+        }
+        drl_threefry2x32_n<kDeriveK>(d.k0, d.k1, x0, x1);
+        const long long o0 = b0 - first, o1 = half + b0 - first;
+        const bool full = b0 + kDeriveK <= d.bmin_k + d.nb_k && b0 + kDeriveK <= half;
+        if (full && o0 >= 0 && o0 + kDeriveK <= end && (((uintptr_t)(keys + o0) & 7) == 0)) *reinterpret_cast<uint2*>(keys + o0) = make_uint2(x0[0], x0[1]);
+        else {
+#pragma unroll
+            for (int i = 0; i < kDeriveK; ++i)
+                if (b0 + i < half && o0 + i >= 0 && o0 + i < end) keys[o0 + i] = x0[i];
+        }
+        if (full && o1 >= 0 && o1 + kDeriveK <= end && (((uintptr_t)(keys + o1) & 7) == 0)) *reinterpret_cast<uint2*>(keys + o1) = make_uint2(x1[0], x1[1]);
+        else {
+#pragma unroll
+            for (int i = 0; i < kDeriveK; ++i)
+                if (b0 + i < half && o1 + i >= 0 && o1 + i < end) keys[o1 + i] = x1[i];
+        }
+        (void)size;
     }
 }
 
@@ -547,6 +607,11 @@ static void carve_layout(DevCfg& c, bool warp_mode, int Q, bool fast, int cta_th
     const int sel_bytes = warp_mode ? 0 : c.sel_hist + 32 + c.sel_cap * 8 + round_up((fast ? 64 : c.sel_maxj) * 2, 16);
     c.off_tile = round_up(c.off_sel + sel_bytes, 128);
     c.group_bytes = c.off_tile + c.tile_bufs * c.tile_stride * (warp_mode ? 1 : cta_threads / 32);
+    c.off_alt = 0;
+    if (warp_mode && kCT) {   // CTA turns: the staged state of a turn is read by the other warps while the next turn is staged
+        c.off_alt = c.group_bytes;
+        c.group_bytes += round_up(Q * c.GS + 256, 128);
+    }
 }
 
 typedef void (*step_fn)(DevCfg, uint8_t*, uint32_t*, const uint32_t*, const int8_t*, float*, uint8_t*, float*,
@@ -569,14 +634,14 @@ static int static_shape(const drl_env* e) {
 }
 template <int NB, class D>
 static step_fn step_warp_q(int q) {
-    return q == DRL_QMAX && q == 8 ? (step_fn)k_step_warp<NB, DRL_QMAX, D> : q == 4 ? (step_fn)k_step_warp<NB, 4, D>
-         : q == 2 ? (step_fn)k_step_warp<NB, 2, D> : (step_fn)k_step_warp<NB, 1, D>;
+    return q == DRL_QMAX && q == 8 ? (step_fn)k_step_warp<NB, DRL_QMAX, D, false, kCT> : q == 4 ? (step_fn)k_step_warp<NB, 4, D, false, kCT>
+         : q == 2 ? (step_fn)k_step_warp<NB, 2, D, false, kCT> : (step_fn)k_step_warp<NB, 1, D, false, kCT>;
 }
 static const void* pick_step(const drl_env* e) {
     if (e->warp_mode) {
         switch (static_shape(e)) {
-            case 1: return (const void*)k_step_warp<2, DRL_QMAX, D943>;
-            case 2: return (const void*)k_step_warp<1, DRL_QMAX, D833>;
+            case 1: return (const void*)k_step_warp<2, DRL_QMAX, D943, false, kCT>;
+            case 2: return (const void*)k_step_warp<1, DRL_QMAX, D833, false, kCT>;
             default: return (const void*)(e->nb == 1 ? step_warp_q<1, DynDims>(e->envs_per_warp) : step_warp_q<2, DynDims>(e->envs_per_warp));
         }
     }
@@ -1435,7 +1500,7 @@ static int launch_derive(drl_env* env, const uint32_t akey[2], const uint32_t ek
     bits_block_range(d.total, d.first, d.count, &d.bmin_a, &d.nb_a);
     d.Ng = Ng; d.off = off; d.Nl = Nl;
     bits_block_range(2 * Ng, 2 * off, 2 * Nl, &d.bmin_k, &d.nb_k);
-    const long long threads = d.nb_a + d.nb_k;
+    const long long threads = (d.nb_a + kDeriveA - 1) / kDeriveA + (d.nb_k + kDeriveK - 1) / kDeriveK;
     return launch(env, "derivation kernel", (const void*)k_derive, (int)((threads + 255) / 256), 256, 0, stream, d,
                   (int8_t*)d_actions, (uint32_t*)d_keys);
 }

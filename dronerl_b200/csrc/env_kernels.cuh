@@ -26,6 +26,17 @@
 namespace drl {
 
 constexpr unsigned FULL = 0xFFFFFFFFu;
+#ifndef DRL_PARK_NOINLINE
+#define DRL_PARK_NOINLINE 0   // A/B: one out-of-line copy of park_pass / select_finish instead of one per call site
+#endif
+#if DRL_PARK_NOINLINE
+#define DRL_PARK_INLINE __noinline__
+#else
+#define DRL_PARK_INLINE __forceinline__
+#endif
+#ifndef DRL_EDGE_WORDS
+#define DRL_EDGE_WORDS 1      // compose_tile: word path for window rows that cross the left / right grid edge (A/B: 0)
+#endif
 enum : int { SKY = 2, STATION = 3, DROPZONE = 4, PACKET = 5 };
 enum : int { A_LEFT = 0, A_DOWN = 1, A_RIGHT = 2, A_UP = 3 };
 #ifndef DRL_CTA_THREADS
@@ -57,6 +68,7 @@ struct DevCfg {
     int tile_bufs;             // tile buffers per warp (1, or 2 alternating)
     // shared-memory carve-up (bytes from the group's base)
     int off_code, off_sdr, off_sdf, off_misc, off_red, off_sel, off_tile;
+    int off_alt;               // warp mode: second staged-state buffer (ground rows | records [32] | charges [32]) for CTA turns
     int sel_hist, sel_cap, sel_maxj;   // CTA mode: bytes of histogram, capacity of the key list, of the rank -> position table
     int group_bytes;           // warp mode: bytes per warp; CTA mode: bytes per CTA
     long long N;               // local envs
@@ -623,7 +635,29 @@ __device__ __forceinline__ void compose_tile(const D& d, const Smem& sm, int d0,
                 cw0 = lut4(__funnelshift_r(w0, w1, sh));
                 cw1 = lut4(__funnelshift_r(w1, w2, sh));
                 cw2 = lut4(__funnelshift_r(w2, w3, sh));
-            } else {
+            } else if (DRL_EDGE_WORDS && gy * G + gx0 >= 0) {
+                // The row crosses the left or right edge of the grid (16 % of the drones at 64x64, r = 5): the same
+                // word loads, started where the row WOULD start -- the cells off the grid then hold bytes of the
+                // neighbouring row (still inside the CTA's shared memory) -- and those cells are overwritten with the
+                // wall code through a byte mask.  (The cell-by-cell loop this replaces was 3.6 % of the C4 kernel.)
+                const int base = gy * G + gx0;
+                const uint32_t* wp = reinterpret_cast<const uint32_t*>(sm.sg + (base & ~3));
+                const uint32_t sh = (uint32_t)(base & 3) * 8u;
+                const uint32_t w0 = wp[0], w1 = wp[1], w2 = wp[2], w3 = wp[3];
+                auto lut4 = [&](uint32_t a) {
+                    const uint32_t t = a | (a >> 4);
+                    return __byte_perm(kLutLo, kLutHi, (t & 0xFFu) | ((t >> 8) & 0xFF00u));
+                };
+                const int L = max(0, -gx0), R = min(W, G - gx0);          // cells [L, R) of the row are on the grid
+                auto low = [](int k) { return (uint32_t)((1ull << (8 * min(max(k, 0), 4))) - 1ull); };   // bytes [0, k) of a word
+                auto wall = [&](uint32_t cw, int j) {                      // word j holds cells [4j, 4j + 4)
+                    const uint32_t m = low(L - 4 * j) | ~low(R - 4 * j);
+                    return (cw & ~m) | (0x05050505u & m);
+                };
+                cw0 = wall(lut4(__funnelshift_r(w0, w1, sh)), 0);
+                cw1 = wall(lut4(__funnelshift_r(w1, w2, sh)), 1);
+                cw2 = wall(lut4(__funnelshift_r(w2, w3, sh)), 2);
+            } else {                                                       // top row and left of the grid: cell by cell
                 const uint8_t* grow = sm.sg + gy * G;
                 for (int wx = 0; wx < W; ++wx) {
                     const int gx = gx0 + wx;
@@ -943,7 +977,7 @@ __device__ __forceinline__ uint32_t select_threshold(int J, int ncand) {
 // vector of (k0, k1), CH at a time with interleaved rounds (block b of worker j: j + count * i), and park the
 // raw words at or above the threshold, with their cells, in ``stage`` (128 entries; *nstage counts them).
 template <int CH, class D>
-__device__ __forceinline__ void park_pass(const D& d, int worker, int count, uint32_t k0, uint32_t k1, uint32_t T0s, uint2* stage,
+__device__ DRL_PARK_INLINE void park_pass(const D& d, int worker, int count, uint32_t k0, uint32_t k1, uint32_t T0s, uint2* stage,
                                           uint32_t* nstage) {
     const int H = d.H(), G2 = d.G2();
     auto park = [&](uint32_t o, int cell) {
@@ -974,8 +1008,11 @@ __device__ __forceinline__ void park_pass(const D& d, int worker, int count, uin
 // Passes 2 and 3: candidates among the parked survivors become keys, the keys are ranked by counting (four
 // threads per key) and sel.pos[0 .. J) receives the winners.  Call with the whole CTA after a barrier that
 // follows pass 1.  Returns false (uniformly) when the result cannot be proven: fewer than J or more than 128 keys.
+// (Tried in round 2 and dropped: 32-bit keys (mantissa - threshold, cell) read four per LDS.128 in the counting loop --
+// bit-exact, 40 % fewer instructions in that loop, but the C4 kernel got SLOWER, 5.41 vs 5.33 ms: its loop body is far
+// larger than the instruction cache and a second code path costs more than the shorter loop saves.)
 template <int T, class D, class P>
-__device__ __forceinline__ bool select_finish(Group<T>& grp, const D& d, const Sel& sel, int tid, const uint2* stage,
+__device__ DRL_PARK_INLINE bool select_finish(Group<T>& grp, const D& d, const Sel& sel, int tid, const uint2* stage,
                                               uint32_t* nstage, int J, P&& pred) {
     const int G2 = d.G2();
     uint32_t* const counter = sel.cnt + 1 + grp.spar;       // two alternating key counters: the one in use is zero
@@ -1018,7 +1055,8 @@ __device__ __forceinline__ bool stream_select(Group<T>& grp, const D& d, const S
                                               int J, int ncand, P&& pred) {
     constexpr int CH = NB < 4 ? NB : 4;
     uint2* const stage = reinterpret_cast<uint2*>(sel.list + 128);
-    park_pass<CH>(d, tid, T, k0, k1, select_threshold(J, ncand), stage, sel.cnt + 3);
+    const uint32_t T0s = select_threshold(J, ncand);
+    park_pass<CH>(d, tid, T, k0, k1, T0s, stage, sel.cnt + 3);
     __syncthreads();
     return select_finish<T>(grp, d, sel, tid, stage, sel.cnt + 3, J, pred);
 }
@@ -1084,7 +1122,8 @@ __device__ __forceinline__ bool env_step_fast(Group<T>& grp, const DevCfg& c, co
         uint32_t* const sbits = reinterpret_cast<uint32_t*>(sm.code);
         if (drone_warp && o.surv) atomicOr(&sbits[(x * G + y) >> 5], 1u << ((x * G + y) & 31));
         const int J = 32 - __clz(mDone);
-        park_pass<(NB < 4 ? NB : 4)>(d, tid, T, rk0, rk1, select_threshold(J, ncand_air), stage_air, nstage_air);
+        const uint32_t T0s_air = select_threshold(J, ncand_air);
+        park_pass<(NB < 4 ? NB : 4)>(d, tid, T, rk0, rk1, T0s_air, stage_air, nstage_air);
         __syncthreads();                                    // also orders the ground writes above
         // no erasing edge on this path, so the skyscrapers are those of the old ground
         auto is_cand = [&](int cell) { return !((sbits[cell >> 5] >> (cell & 31)) & 1u) && sm.sg[cell] != SKY && cell != G2 - 1; };

@@ -27,26 +27,41 @@ __device__ __forceinline__ int zero_bytes16(const uint4& v) {
 
 // HP: instance for drl_step_host's single-launch pipeline (input flags / completion counters compiled in only there:
 // the step loop is instruction-cache bound and every extra line in it costs time).
-template <int NB, int Q, class D, bool HP = false>
+// CT ("CTA turns"): instead of every warp drawing its own ticket, the CTA draws one ticket = 8 * Q consecutive envs per
+// turn.  Phase A: warp w steps envs [Q w, Q w + Q) of the turn exactly as in the per-warp form (state traffic in
+// Q-env blocks).  One barrier.  Phase B: warp w composes and bulk-stores the tiles of envs w, w + 8, w + 16, ... of the
+// turn, read from the other warps' staged state -- so the CTA's eight warps write eight NEIGHBOURING tiles at the same
+// time (tools/micro/layout_bench.cu, layout 2: 0.819 ms against 0.846 for per-warp tickets under a synthetic compute
+// load).  MEASURED SLOWER in this kernel (0.961 vs 0.867 ms per 1M envs: the turn waits for its slowest warp), so it is
+// compiled in only with -DDRL_CTA_TURNS=1; kept as the A/B record of that lever.  The staged state (ground rows, drone records, charges) is double-buffered by turn parity, so one barrier
+// per turn is enough: a warp can only overwrite buffer p two turns later, after the next barrier, which every warp
+// reaches only when its phase B of this turn is done.
+template <int NB, int Q, class D, bool HP = false, bool CT = false>
 __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsigned char* base, uint8_t* __restrict__ ground,
                                                uint32_t* __restrict__ drones, const uint32_t* __restrict__ keys,
                                                const int8_t* __restrict__ actions, float* __restrict__ rewards,
                                                uint8_t* __restrict__ dones, float* __restrict__ obs,
                                                unsigned long long* __restrict__ stats, long long first_group,
-                                               long long total_warps, unsigned* __restrict__ queue) {
+                                               long long total_warps, unsigned* __restrict__ queue,
+                                               unsigned char* cta_smem = nullptr) {
+    static_assert(!(HP && CT), "the host-pipeline instance keeps per-warp tickets (its abort path cannot sit behind a CTA barrier)");
     constexpr int S = 32 / Q;
     constexpr uint32_t SM = Q == 1 ? FULL : ((1u << S) - 1u);
     const int lane = threadIdx.x & 31;
     const int sub = lane / S, li = lane % S;
     const int G = d.G(), G2 = d.G2(), GS = d.GS(), n = d.n();
     const int CP = (G2 + 15) & ~15;
-    uint8_t* const sg_all = base;
+    // staged state of this warp's envs: buffer 0 at the front of the warp's region, buffer 1 (CT only) at off_alt
+    uint8_t* sg_all = base;
     uint8_t* const code_all = base + c.off_code;
-    uint32_t* const sdr = reinterpret_cast<uint32_t*>(base + c.off_sdr);
-    float* const sdf = reinterpret_cast<float*>(base + c.off_sdf);
+    uint32_t* sdr = reinterpret_cast<uint32_t*>(base + c.off_sdr);
+    float* sdf = reinterpret_cast<float*>(base + c.off_sdf);
     int* const zcs = reinterpret_cast<int*>(base + c.off_misc);
     float* const tile = reinterpret_cast<float*>(base + c.off_tile);
-    uint8_t* const sg = sg_all + sub * GS;       // this lane's env
+    uint8_t* sg = sg_all + sub * GS;             // this lane's env
+    const int warp = threadIdx.x >> 5;
+    volatile unsigned* const tk = reinterpret_cast<volatile unsigned*>(cta_smem + c.off_misc + 32);   // CT: the CTA's tickets, [2]
+    int sbuf = 0;                                // CT: state buffer of the current turn
     Group<32> grp{nullptr};
     {   // survivor-mark scratch starts (and is always restored to) all zero
         uint32_t* w = reinterpret_cast<uint32_t*>(code_all);
@@ -133,6 +148,15 @@ __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsi
         if (lane == 0) t = atomicAdd(queue, 1u);
         return total_warps + (long long)__shfl_sync(FULL, t, 0);
     };
+    // CT: thread 0 draws the CTA's ticket into tk[slot]; everybody reads it after the next barrier.  A turn with
+    // ticket t is groups 8 t + warp (a group = Q envs), offset by the statically assigned first turns.
+    auto cta_draw = [&](int slot) {
+        if (CT && queue != nullptr && threadIdx.x == 0) tk[slot] = atomicAdd(queue, 1u);
+    };
+    auto cta_next = [&](long long after, int slot) -> long long {
+        if (queue == nullptr) return after + total_warps;
+        return total_warps + (long long)tk[slot] * kWarpsPerBlock + warp;
+    };
     // Host pipeline (HP): a finished group is reported to the copy stream one group later, right before the next
     // write-back -- by then its stores (and its tile stores) have long completed, so the fence that orders them before
     // the counter update has nothing to wait for (reporting at the end of the group's own iteration cost 1.1 us per
@@ -149,13 +173,32 @@ __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsi
     };
     long long g = first_group;
     prefetch(g);
-    long long gn = ticket(g), gnn = 0;
-    for (; g * Q < c.N && !(HP && aborted); g = gn, gn = gnn) {
+    long long gn, gnn = 0;
+    int tslot = 0;
+    if constexpr (CT) {
+        cta_draw(0);
+        __syncthreads();
+        gn = cta_next(g, 0);
+        tslot = 1;
+    } else {
+        gn = ticket(g);
+    }
+    // CT: every warp of the CTA takes the same number of turns (the condition is the turn's first env), warps whose
+    // own envs lie past the end idle through phase A
+    for (; (CT ? (g - warp) * Q < c.N : g * Q < c.N) && !(HP && aborted); g = gn, gn = gnn) {
         const long long e0 = g * Q;
-        const int nq = (int)min((long long)Q, c.N - e0);
+        const int nq = (int)max(0ll, min((long long)Q, c.N - e0));
         const GroupInputs<NV> cur = nxt;
         prefetch(gn);
-        gnn = ticket(gn);
+        if constexpr (CT) {
+            cta_draw(tslot);
+            sg_all = sbuf ? base + c.off_alt : base;
+            sdr = reinterpret_cast<uint32_t*>(sbuf ? base + c.off_alt + Q * GS : base + c.off_sdr);
+            sdf = reinterpret_cast<float*>(sbuf ? base + c.off_alt + Q * GS + 128 : base + c.off_sdf);
+            sg = sg_all + sub * GS;
+        } else {
+            gnn = ticket(gn);
+        }
         const bool act_env = sub < nq;
         const bool isd = act_env && li < n;
         const long long e = e0 + sub;
@@ -382,16 +425,44 @@ __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsi
                 sdr[lane] = (rec & 0xFF01FFFFu) | (((31 - __clz(og)) == lane) ? (1u << 17) : 0u);
                 sdf[lane] = __fdiv_rn((float)ch, 100.0f);
             }
-            __syncwarp();
-            for (int q = 0; q < nq; ++q) {
-                Smem smq;
-                smq.sg = sg_all + q * GS;
-                smq.code = code_all + q * CP;
-                smq.sdr = sdr + q * S;
-                smq.sdf = sdf + q * S;
-                smq.misc = nullptr;
-                obs_tiles(d, c, smq, obs, e0 + q, tile, tsel, 0, 1, lane);
+            if constexpr (!CT) {
+                __syncwarp();
+                for (int q = 0; q < nq; ++q) {
+                    Smem smq;
+                    smq.sg = sg_all + q * GS;
+                    smq.code = code_all + q * CP;
+                    smq.sdr = sdr + q * S;
+                    smq.sdf = sdf + q * S;
+                    smq.misc = nullptr;
+                    obs_tiles(d, c, smq, obs, e0 + q, tile, tsel, 0, 1, lane);
+                }
             }
+        }
+        if constexpr (CT) {
+            __syncthreads();                     // phase A of every warp is staged; the next turn's ticket is published
+            gnn = cta_next(gn, tslot);
+            tslot ^= 1;
+            if (obs != nullptr) {
+                const long long c0 = (g - warp) * Q;                      // first env of the CTA's turn
+                const int so = sbuf ? c.off_alt : 0;
+                const int ro = sbuf ? c.off_alt + Q * GS : c.off_sdr, fo = sbuf ? c.off_alt + Q * GS + 128 : c.off_sdf;
+#pragma unroll 1
+                for (int j = 0; j < Q; ++j) {
+                    const int i = warp + kWarpsPerBlock * j;              // env i of the turn: staged by warp i / Q in slot i % Q
+                    const long long e = c0 + i;
+                    if (e >= c.N) break;
+                    const int ow = i / Q, oq = i - ow * Q;
+                    unsigned char* const ob = cta_smem + (size_t)ow * c.group_bytes;
+                    Smem smq;
+                    smq.sg = ob + so + oq * GS;
+                    smq.code = nullptr;
+                    smq.sdr = reinterpret_cast<uint32_t*>(ob + ro) + oq * S;
+                    smq.sdf = reinterpret_cast<float*>(ob + fo) + oq * S;
+                    smq.misc = nullptr;
+                    obs_tiles(d, c, smq, obs, e, tile, tsel, 0, 1, lane);
+                }
+            }
+            sbuf ^= 1;
         }
         env_steps += nq;
         if (HP) { sig_chunk = (int)(e0 >> c.chunk_shift); sig_n = nq; }   // reported at the next group's write-back

@@ -90,8 +90,8 @@ def test_host_pipeline_instance_reads_actions_coherently():
             fn = m.group(1)
         elif fn and re.search(r'LDG\.E\.[US]8', line):
             loads.setdefault(fn, []).append(line)
-    hp = {f: v for f, v in loads.items() if 'k_step_warp' in f and 'ELb1EE' in f}
-    plain = {f: v for f, v in loads.items() if 'k_step_warp' in f and 'ELb0EE' in f}
+    hp = {f: v for f, v in loads.items() if 'k_step_warp' in f and 'ELb1ELb0EE' in f}
+    plain = {f: v for f, v in loads.items() if 'k_step_warp' in f and 'ELb0ELb' in f}
     assert hp and plain
     for f, v in hp.items():
         assert all('CONSTANT' not in x and 'STRONG' in x for x in v), (f, v)

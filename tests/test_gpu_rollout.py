@@ -76,6 +76,28 @@ def test_two_run_calls_equal_one(c_oracle):
     assert (a.rng[0], a.rng[1]) == (b.rng[0], b.rng[1])
 
 
+def test_three_odd_slices_equal_unsharded_rollout(c_oracle):
+    """Three slices of 1,001 envs x 3 drones: 9,009 actions in total (odd: the zero pad counter of random_bits), slice
+    offsets 3,003 / 6,006 actions (not multiples of the derivation kernel's 4-block / 2-block packets, one slice
+    straddling the middle of the vector): the merged derivation launch takes its unaligned / partial paths."""
+    import dronerl_b200 as drl
+    from dronerl_b200.rollout import ShardedRollout
+    from oracle.rollout_ref import RolloutRef
+    p = drl.DroneEnvParams(grid_size=8, n_drones=3, window_radius=3)
+    N = 3003
+    parts = [ShardedRollout(p, N, rank=g, world=3, seed=8, reset_every=7) for g in range(3)]
+    ref = RolloutRef(oracle_params(p), N, seed=8, reset_every=7)
+    for q in parts:
+        q.run(17)
+    ref.run(17)
+    np.testing.assert_array_equal(torch.cat([q.actions for q in parts]).cpu().numpy().astype(np.int32), ref.actions)
+    np.testing.assert_array_equal(torch.cat([q.rewards for q in parts]).cpu().numpy().view(np.uint32), ref.rewards.view(np.uint32))
+    np.testing.assert_array_equal(torch.cat([q.obs for q in parts]).cpu().numpy().view(np.uint32), ref.obs().view(np.uint32))
+    got = [sum(v) for v in zip(*[q.local_stats() for q in parts])]
+    from dronerl_b200 import _lib
+    assert dict(zip(_lib.STAT_NAMES, got)) == ref.stats
+
+
 @pytest.mark.parametrize('G,n,r,N', [(9, 4, 3, 4096), (12, 6, 2, 192)])
 def test_two_slices_equal_unsharded_rollout(c_oracle, G, n, r, N):
     """world = 2 in one process: each slice runs the driver with its own env_offset; concatenated slices == the
