@@ -962,6 +962,10 @@ int drl_create(const drl_config* cfg, drl_env** out) {
     c.obs_n = n;
     c.ntiles = (n + c.tile_drones - 1) / c.tile_drones;
     c.tile_stride = round_up(c.tile_drones * cell_bytes, 128);
+    e->envs_per_warp = !e->warp_mode ? 1 : n <= 4 ? DRL_QMAX : n <= 8 ? 4 : n <= 16 ? 2 : 1;
+    // pairs of envs per bulk store when one env's windows are an odd multiple of 8 bytes (see DevCfg::tile_pair)
+    c.tile_pair = e->warp_mode && c.ntiles == 1 && e->envs_per_warp >= 2 && ((n * cell_bytes) % 16) == 8 && !getenv("DRL_NO_TILE_PAIR");
+    if (c.tile_pair) c.tile_stride = round_up(2 * n * cell_bytes, 128);
     c.tile_bufs = 1;
     if (const char* tb = getenv("DRL_TILE_BUFS")) c.tile_bufs = (e->warp_mode && tb[0] == '2') ? 2 : 1;   // A/B switch
     {   // every other A/B switch: read here, once per handle

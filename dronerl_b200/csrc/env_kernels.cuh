@@ -26,14 +26,6 @@
 namespace drl {
 
 constexpr unsigned FULL = 0xFFFFFFFFu;
-#ifndef DRL_PARK_NOINLINE
-#define DRL_PARK_NOINLINE 0   // A/B: one out-of-line copy of park_pass / select_finish instead of one per call site
-#endif
-#if DRL_PARK_NOINLINE
-#define DRL_PARK_INLINE __noinline__
-#else
-#define DRL_PARK_INLINE __forceinline__
-#endif
 #ifndef DRL_EDGE_WORDS
 #define DRL_EDGE_WORDS 1      // compose_tile: word path for window rows that cross the left / right grid edge (A/B: 0)
 #endif
@@ -66,6 +58,8 @@ struct DevCfg {
     int obs_n;                 // drones whose windows are rendered (the first obs_n; n by default)
     int tile_stride;           // bytes reserved per obs tile buffer
     int tile_bufs;             // tile buffers per warp (1, or 2 alternating)
+    int tile_pair;             // warp mode: an env's windows are an odd multiple of 8 bytes (odd n_drones): two consecutive
+                               // envs are composed side by side and leave as ONE 16-byte-aligned bulk store
     // shared-memory carve-up (bytes from the group's base)
     int off_code, off_sdr, off_sdf, off_misc, off_red, off_sel, off_tile;
     int off_alt;               // warp mode: second staged-state buffer (ground rows | records [32] | charges [32]) for CTA turns
@@ -558,8 +552,11 @@ __device__ __forceinline__ void tile_store(float* gdst, const float* ssrc, int b
 // The one-hot tensor is ~90 % zeros, so the tile is zero-filled with 128-bit stores and only the
 // non-zero entries are scattered: one lane per window ROW walks its W cells (ground class -> one
 // store), then one lane per (viewer, other drone) pair marks channels 0 and 4.
+// ``fill``: bytes of the tile buffer to wait for and zero before composing (-1: this tile's own size; 0: the caller
+// already did both -- the second env of a pair).
 template <class D>
-__device__ __forceinline__ void compose_tile(const D& d, const Smem& sm, int d0, int d1, float* tile, int lane, int bufs) {
+__device__ __forceinline__ void compose_tile(const D& d, const Smem& sm, int d0, int d1, float* tile, int lane, int bufs,
+                                             int fill = -1) {
     const int nd = d1 - d0;
     // ground value -> channel: 0 -> none, SKY 2 -> 5, STATION 3 -> 3, DROPZONE 4 -> 2, PACKET 5 -> 1
     constexpr uint32_t kChan = (5u << 8) | (3u << 12) | (2u << 16) | (1u << 20);
@@ -673,10 +670,12 @@ __device__ __forceinline__ void compose_tile(const D& d, const Smem& sm, int d0,
     } else if (packed64) {
         if (lane < items) pw = row_codes(lane, 0ull);
     }
-    tile_wait_reusable(lane, bufs);
-    const int vecs = (nd * d.W2() * 24 + 15) >> 4;          // tile buffers are padded to 128 B
-    float4* t4 = reinterpret_cast<float4*>(tile);
-    for (int i = lane; i < vecs; i += 32) t4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (fill != 0) {
+        tile_wait_reusable(lane, bufs);
+        const int vecs = ((fill < 0 ? nd * d.W2() * 24 : fill) + 15) >> 4;          // tile buffers are padded to 128 B
+        float4* t4 = reinterpret_cast<float4*>(tile);
+        for (int i = lane; i < vecs; i += 32) t4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
     __syncwarp();
     if (words) {
         if (lane < items) {
@@ -977,7 +976,7 @@ __device__ __forceinline__ uint32_t select_threshold(int J, int ncand) {
 // vector of (k0, k1), CH at a time with interleaved rounds (block b of worker j: j + count * i), and park the
 // raw words at or above the threshold, with their cells, in ``stage`` (128 entries; *nstage counts them).
 template <int CH, class D>
-__device__ DRL_PARK_INLINE void park_pass(const D& d, int worker, int count, uint32_t k0, uint32_t k1, uint32_t T0s, uint2* stage,
+__device__ __forceinline__ void park_pass(const D& d, int worker, int count, uint32_t k0, uint32_t k1, uint32_t T0s, uint2* stage,
                                           uint32_t* nstage) {
     const int H = d.H(), G2 = d.G2();
     auto park = [&](uint32_t o, int cell) {
@@ -1008,11 +1007,13 @@ __device__ DRL_PARK_INLINE void park_pass(const D& d, int worker, int count, uin
 // Passes 2 and 3: candidates among the parked survivors become keys, the keys are ranked by counting (four
 // threads per key) and sel.pos[0 .. J) receives the winners.  Call with the whole CTA after a barrier that
 // follows pass 1.  Returns false (uniformly) when the result cannot be proven: fewer than J or more than 128 keys.
+// (Also tried and dropped: park_pass / select_finish as single out-of-line copies instead of one per call site: 10 % less
+// code, 7.48 vs 5.24 ms -- the calls spill the interleaved hash state.)
 // (Tried in round 2 and dropped: 32-bit keys (mantissa - threshold, cell) read four per LDS.128 in the counting loop --
 // bit-exact, 40 % fewer instructions in that loop, but the C4 kernel got SLOWER, 5.41 vs 5.33 ms: its loop body is far
 // larger than the instruction cache and a second code path costs more than the shorter loop saves.)
 template <int T, class D, class P>
-__device__ DRL_PARK_INLINE bool select_finish(Group<T>& grp, const D& d, const Sel& sel, int tid, const uint2* stage,
+__device__ __forceinline__ bool select_finish(Group<T>& grp, const D& d, const Sel& sel, int tid, const uint2* stage,
                                               uint32_t* nstage, int J, P&& pred) {
     const int G2 = d.G2();
     uint32_t* const counter = sel.cnt + 1 + grp.spar;       // two alternating key counters: the one in use is zero

@@ -425,7 +425,27 @@ __device__ __forceinline__ void step_warp_body(const DevCfg& c, const D& d, unsi
                 sdr[lane] = (rec & 0xFF01FFFFu) | (((31 - __clz(og)) == lane) ? (1u << 17) : 0u);
                 sdf[lane] = __fdiv_rn((float)ch, 100.0f);
             }
-            if constexpr (!CT) {
+            if (!CT && c.tile_pair) {
+                // odd n_drones: env blocks of the obs tensor are only 8-byte aligned, pairs of them (the group's first
+                // env index is even) are 16-byte aligned -> compose two envs side by side, one bulk store per pair
+                __syncwarp();
+                const int B = d.obs_n() * d.W2() * 24;
+                for (int q = 0; q < nq; q += 2) {
+                    const bool two = q + 1 < nq;
+                    float* buf = tile + tsel * (c.tile_stride >> 2);
+                    tsel ^= (c.tile_bufs - 1);
+                    Smem smq;
+                    smq.code = nullptr;
+                    smq.misc = nullptr;
+                    smq.sg = sg_all + q * GS; smq.sdr = sdr + q * S; smq.sdf = sdf + q * S;
+                    compose_tile(d, smq, 0, d.obs_n(), buf, lane, c.tile_bufs, two ? 2 * B : B);
+                    if (two) {
+                        smq.sg = sg_all + (q + 1) * GS; smq.sdr = sdr + (q + 1) * S; smq.sdf = sdf + (q + 1) * S;
+                        compose_tile(d, smq, 0, d.obs_n(), buf + (B >> 2), lane, c.tile_bufs, 0);
+                    }
+                    tile_store(obs + (size_t)(e0 + q) * (size_t)(B >> 2), buf, two ? 2 * B : B, lane);
+                }
+            } else if constexpr (!CT) {
                 __syncwarp();
                 for (int q = 0; q < nq; ++q) {
                     Smem smq;
