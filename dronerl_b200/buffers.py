@@ -46,9 +46,13 @@ class ReplayBuffer:
         Updates the storage and the counters IN PLACE (graph-capturable) and returns the same state."""
         k = next(iter(experiences.values())).shape[0]
         dev = state.current_idx.device
-        idx = (state.current_idx + torch.arange(k, device=dev)) % self.buffer_size
+        # More experiences than slots: the ring indices repeat, and the reference's ``.at[indices].set`` keeps the LAST
+        # write per slot -- i.e. only the last ``buffer_size`` experiences survive, at the same slots.  index_copy_ with
+        # duplicate indices is nondeterministic, so write exactly those.
+        first = max(k - self.buffer_size, 0)
+        idx = (state.current_idx + torch.arange(first, k, device=dev)) % self.buffer_size
         for name, field in state.experiences.items():
-            field.index_copy_(0, idx, experiences[name].to(field.dtype))
+            field.index_copy_(0, idx, experiences[name][first:].to(field.dtype))
         state.current_idx.copy_((state.current_idx + k) % self.buffer_size)
         state.current_size.copy_(torch.clamp(state.current_size + k, max=self.buffer_size))
         return state
@@ -56,9 +60,11 @@ class ReplayBuffer:
     def sample(self, state: BufferState, generator=None) -> Dict[str, torch.Tensor]:
         """buffers.py:79-90: ``sample_batch_size`` uniform indices in ``[0, current_size)`` (with replacement)."""
         dev = state.current_idx.device
-        u = torch.rand(self.sample_batch_size, device=dev, generator=generator)
-        idx = torch.clamp((u * state.current_size).to(torch.int64), max=self.buffer_size - 1)
-        idx = torch.minimum(idx, torch.clamp(state.current_size - 1, min=0))
+        # integer draws (the reference uses jax.random.randint): 63 random bits modulo the size -- every slot reachable
+        # at any buffer size, modulo bias < 2^-40; no float32 rounding (floor(rand_f32 * size) cannot reach all slots
+        # beyond 2^24 entries and is biased below that)
+        bits = torch.empty(self.sample_batch_size, dtype=torch.int64, device=dev).random_(generator=generator)
+        idx = bits % torch.clamp(state.current_size, min=1)
         return {k: v.index_select(0, idx) for k, v in state.experiences.items()}
 
     def can_sample(self, state: BufferState) -> bool:

@@ -5,8 +5,9 @@
 // jax.random.split / uniform at /root/reference/jax_impl/env/env.py:54,78,107-118,197,224.
 // This is the published Random123 Threefry-2x32-20 block function with jax's
 // key schedule (rotations 13,15,26,6 / 17,29,16,24; parity 0x1BD11BDA; five key
-// injections) -- known answers are checked in tests/test_abi_host.py and on the
-// device in tests/test_gpu_prng.py.
+// injections) -- known answers are checked on the host in tests/test_abi.py
+// (drl_prng_key / drl_split2 vs oracle/jaxrand.py) and tests/test_oracle_reference_kats.py, and on the device in
+// tests/test_gpu_parity.py::test_split_and_randint_slices_match_oracle and tests/test_gpu_trainer.py.
 #pragma once
 #include <stdint.h>
 

@@ -201,7 +201,13 @@ class OnDeviceDQNTrainer:
         # epsilon decay on env 0 / drone 0 done when no interval is set (dqn.py:190-199)
         if ag.epsilon_decay_every is None:
             dec = torch.clamp(self.epsilon * ag.epsilon_decay, min=ag.epsilon_end)
-            self.epsilon.copy_(torch.where(self.dones[0, 0] != 0, dec, self.epsilon))
+            # the reference looks at GLOBAL env 0 (dones[0]); under data parallelism that env lives on rank 0, so its
+            # flag is broadcast -- every rank decays in the same steps and epsilon stays identical across ranks
+            flag = (self.dones[0, 0] != 0).to(torch.int32)
+            if self.world > 1:
+                import torch.distributed as dist
+                dist.broadcast(flag, src=0)
+            self.epsilon.copy_(torch.where(flag != 0, dec, self.epsilon))
         # next_obs becomes obs (:115 carry)
         self.obs.copy_(self.next_obs)
 

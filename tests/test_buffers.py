@@ -71,3 +71,30 @@ def test_add_many_experiences():                        # :82-128
     for i in range(2):
         for k in ex:
             assert torch.all(st.experiences[k][i] == ex[k] + 3 + i)
+
+
+def test_add_many_more_experiences_than_slots_keeps_the_last_writes():
+    """k > buffer_size: the ring indices repeat and the reference's ``.at[indices].set`` keeps the last write per slot
+    (jax_impl/buffers.py:57-77) -- deterministically, unlike index_copy_ with duplicate indices."""
+    import torch
+    from dronerl_b200.buffers import ReplayBuffer
+    buf = ReplayBuffer(buffer_size=8, sample_batch_size=4)
+    st = buf.init({'x': torch.zeros((), dtype=torch.int64)})
+    buf.add_many(st, {'x': torch.arange(3)})                       # current_idx = 3
+    buf.add_many(st, {'x': torch.arange(100, 121)})                # 21 experiences into 8 slots
+    want = torch.zeros(8, dtype=torch.int64)
+    for j, v in enumerate(range(100, 121)):                        # sequential scatter, last write wins
+        want[(3 + j) % 8] = v
+    assert torch.equal(st.experiences['x'], want)
+    assert int(st.current_idx) == (3 + 21) % 8 and int(st.current_size) == 8
+
+
+def test_sample_uses_integer_draws_and_reaches_every_slot():
+    import torch
+    from dronerl_b200.buffers import ReplayBuffer
+    buf = ReplayBuffer(buffer_size=16, sample_batch_size=4096)
+    st = buf.init({'x': torch.zeros((), dtype=torch.int64)})
+    buf.add_many(st, {'x': torch.arange(11)})
+    g = torch.Generator().manual_seed(0)
+    got = buf.sample(st, generator=g)['x']
+    assert set(got.tolist()) == set(range(11))                     # only filled slots, all of them
