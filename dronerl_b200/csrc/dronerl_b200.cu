@@ -315,6 +315,188 @@ k_step_fast(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint
     }
 }
 
+// ---- CTA mode, fast path, WARP-SPECIALISED (round 2) ---------------------------------------------------------------
+//
+// k_step_fast runs the phases of one env one after the other with all four warps: drone phase, hashing + parking +
+// selection (ALU-pipe bound: 2,048 threefry blocks per noise vector, ~1.9 vectors per env at 64x64 / 32 drones),
+// then write-back + 16 observation tiles (shared-memory stores, address arithmetic, bulk stores).  The ALU pipe is the
+// busiest unit of that kernel (67 %) and issue is 72 % active: hashing (2.5 ms of ALU time per launch) and the rest
+// (2.7 ms of issue time) add up to the measured 5.24 ms -- they hardly overlap, because which phase each of an SM's
+// seven CTAs is in is left to chance.  Here the overlap is built in: in every CTA warps 0-1 ("steppers") run the step of
+// env e+1 while warps 2-3 ("renderers") write back and render env e, so every SM always has 14 warps feeding the ALU
+// pipe and 14 warps using the slots it leaves free.  MEASURED (tools/ab_c4_split.sh): bit-exact on the whole parity
+// suite, but 6.71 ms per launch against 5.25 for k_step_fast -- the model above is wrong: the step is bound by the
+// LATENCY of its dependent phases (parking atomics, selection, barriers), which two warps per env take twice as long
+// to walk through, while the renderers wait; at a register-limited 28 warps per SM the SM gains nothing from the split.
+// Kept behind DRL_FAST_SPLIT=1 as the record of that experiment.  Hand-over through a ring of three staged envs in shared memory
+// (ground, final drone records) with named barriers: full[b] (steppers arrive, renderers wait) and empty[b] (the other
+// way round); the steppers prefetch the NEXT env's ground into the third slot with cp.async while they step.
+constexpr int kRing = 3;
+enum : int { BAR_FULL0 = 1, BAR_EMPTY0 = 4, BAR_STEP = 7, BAR_REND = 8 };
+
+__device__ __forceinline__ void bar_sync_n(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+__device__ __forceinline__ void bar_arrive_n(int id, int n) {
+    __threadfence_block();          // the arriving thread's shared-memory writes are ordered before the arrival
+    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory");
+}
+
+template <int NB, class D>
+__global__ void __launch_bounds__(kFastThreads, DRL_FAST_MIN_BLOCKS)
+k_step_fast2(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint32_t* __restrict__ drones,
+             const uint32_t* __restrict__ keys, const int8_t* __restrict__ actions, float* __restrict__ rewards,
+             uint8_t* __restrict__ dones, float* __restrict__ obs, unsigned long long* __restrict__ stats, int* redo, int* redo_list,
+             unsigned* __restrict__ queue) {
+    static_assert(kFastThreads == 128, "two stepping warps + two rendering warps");
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr int TS = 64;                                  // threads per role
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const D d{c};
+    const int GS = d.GS(), nvec = GS >> 4, n = d.n();
+    auto ring = [&](int b) { return smem_raw + c.off_ring + (size_t)b * c.ring_stride; };
+    auto ring_rec = [&](int b) { return reinterpret_cast<uint32_t*>(ring(b) + GS); };
+    auto ring_meta = [&](int b) { return reinterpret_cast<int*>(ring(b) + GS + 384); };      // e (lo, hi), ok
+
+    if (warp >= 2) {
+        // ================= renderers: write-back + observations of the envs the steppers hand over =================
+        const int rt = threadIdx.x - TS, rw = warp - 2;
+        float* tile = reinterpret_cast<float*>(smem_raw + c.off_tile + (size_t)rw * c.tile_bufs * c.tile_stride);
+        int tsel = 0;
+        for (int i = 0;; ++i) {
+            const int b = i % kRing;
+            bar_sync_n(BAR_FULL0 + b, 2 * TS);
+            const int* meta = ring_meta(b);
+            const long long e = (long long)(unsigned)meta[0] | ((long long)meta[1] << 32);
+            if (e < 0) break;                               // the steppers are done
+            if (meta[2]) {                                  // (0: the env went to the redo list untouched)
+                Smem sm;
+                sm.sg = ring(b);
+                sm.code = nullptr;
+                sm.sdr = ring_rec(b) + 32;
+                sm.sdf = reinterpret_cast<float*>(ring_rec(b) + 64);
+                sm.misc = nullptr;
+                for (int v = rt; v < nvec; v += TS)
+                    reinterpret_cast<uint4*>(ground + e * GS)[v] = reinterpret_cast<const uint4*>(sm.sg)[v];
+                if (rw == 0) {
+                    const uint32_t rec = lane < n ? ring_rec(b)[lane] : 0u;
+                    if (lane < n) drones[e * n + lane] = rec;
+                    if (obs != nullptr) obs_publish(d, sm, lane, rec);
+                }
+                if (obs != nullptr) {
+                    bar_sync_n(BAR_REND, TS);
+                    obs_tiles(d, c, sm, obs, e, tile, tsel, rw, 2, lane);
+                }
+            }
+            bar_arrive_n(BAR_EMPTY0 + b, 2 * TS);           // (tiles are composed from the slot, not stored from it)
+        }
+        tile_drain(lane);
+        return;
+    }
+
+    // ================= steppers =====================================================================================
+    const int tid = threadIdx.x;                            // 0 .. 63
+    Smem sm;
+    sm.code = smem_raw + c.off_code;
+    sm.sdr = nullptr;
+    sm.sdf = nullptr;
+    sm.misc = reinterpret_cast<uint32_t*>(smem_raw + c.off_misc);
+    int* const red = reinterpret_cast<int*>(smem_raw + c.off_red);
+    Group<TS> grp{nullptr};
+    const Sel sel = carve_sel(smem_raw, c);
+    {
+        uint32_t* w = reinterpret_cast<uint32_t*>(sm.code);
+        for (int i = tid; i < (c.off_misc - c.off_code) >> 2; i += TS) w[i] = 0u;
+    }
+    if (tid == 0) sel.cnt[1] = sel.cnt[2] = sel.cnt[3] = sel.cnt[4] = 0u;
+    Stats st;
+    unsigned env_steps = 0;
+    auto stage = [&](long long e, int b) {                  // cp.async the ground of env e into ring slot b
+        if (e < c.N) {
+            const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(ring(b));
+            for (int v = tid; v < nvec; v += TS)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sbase + 16u * v), "l"(ground + e * GS + 16 * v) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    uint32_t nx_rec = 0;
+    int nx_act = 4;
+    uint2 nx_key = make_uint2(0, 0);
+    auto fetch = [&](long long e) {
+        if (e < c.N) {
+            if (!c.key_mode) nx_key = *reinterpret_cast<const uint2*>(keys + 2 * e);
+            if (tid < n) {
+                nx_rec = drones[e * n + tid];
+                if (!c.act_mode) nx_act = (int)actions[e * n + tid];
+            }
+        }
+    };
+    long long e = blockIdx.x, en = 0;
+    unsigned tk = 0;
+    if (queue != nullptr && tid == 0) tk = atomicAdd(queue, 1u);
+    stage(e, 0);
+    fetch(e);
+    int i = 0;
+    for (; e < c.N; e = en, ++i) {
+        const int b = i % kRing, bn = (i + 1) % kRing;
+        if (queue != nullptr && tid == 0) {
+            sm.misc[10] = tk;                               // published by the barrier below
+            tk = atomicAdd(queue, 1u);
+        }
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        bar_sync_n(BAR_STEP, TS);                           // the slot's ground has landed (every stepper's copies)
+        en = queue != nullptr ? (long long)gridDim.x + (long long)sm.misc[10] : e + gridDim.x;
+        // the next env's ground goes into the slot after this one -- free once the renderers are done with env i - 2
+        if (i + 1 >= kRing) bar_sync_n(BAR_EMPTY0 + bn, 2 * TS);
+        stage(en, bn);
+        sm.sg = ring(b);
+        int zc = 0;
+        for (int v = tid; v < nvec; v += TS) zc += zero_bytes16(reinterpret_cast<const uint4*>(sm.sg)[v]);
+        zc = (int)__reduce_add_sync(FULL, (unsigned)zc);
+        if (lane == 0) red[warp] = zc;
+        uint32_t rec = nx_rec;
+        int act = nx_act;
+        if (c.act_mode && tid < n) act = derive_action(c, e, tid);
+        if (c.key_mode && warp == 1 && lane < 2) sm.misc[8 + lane] = derive_key_word(c, e, lane);
+        const uint2 key_e = nx_key;
+        bar_sync_n(BAR_STEP, TS);
+        const int F0 = red[0] + red[1] - (GS - d.G2());
+        const uint2 kk = c.key_mode ? make_uint2(sm.misc[8], sm.misc[9]) : key_e;
+        const Stats before = st;
+        const bool ok = env_step_fast<TS, NB, BAR_STEP>(grp, c, d, sm, sel, F0, rec, act, kk.x, kk.y, rewards + e * n, dones + e * n, st);
+        fetch(en);
+        if (tid < n) ring_rec(b)[tid] = rec;
+        if (tid == 0) {
+            int* meta = ring_meta(b);
+            meta[0] = (int)(unsigned)(e & 0xFFFFFFFFll);
+            meta[1] = (int)(e >> 32);
+            meta[2] = ok ? 1 : 0;
+            if (ok) ++env_steps;
+            else redo_list[atomicAdd(redo, 1)] = (int)e;
+        }
+        if (!ok) st = before;
+        bar_arrive_n(BAR_FULL0 + b, 2 * TS);                // hand the env to the renderers
+    }
+    {   // end marker for the renderers in the next slot: it is free -- its empty barrier was consumed in the last
+        // iteration, when the (non-existent) next env would have been prefetched into it
+        const int b = i % kRing;
+        asm volatile("cp.async.wait_group 0;" ::: "memory");    // (the empty prefetch group of the last iteration)
+        if (tid == 0) {
+            int* meta = ring_meta(b);
+            meta[0] = -1;
+            meta[1] = -1;
+            meta[2] = 0;
+        }
+        bar_arrive_n(BAR_FULL0 + b, 2 * TS);
+    }
+    if (warp == 0) flush_stats(st, env_steps, stats, lane);
+    if (queue != nullptr && tid == 0) {
+        __threadfence();
+        if (atomicAdd(queue + 1, 1u) == gridDim.x - 1u) {
+            queue[0] = 0u;
+            queue[1] = 0u;
+        }
+    }
+}
+
 template <int NB>
 __global__ void __launch_bounds__(kCtaThreads)
 k_reset_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint32_t* __restrict__ drones,
@@ -546,6 +728,7 @@ struct drl_env {
     cudaEvent_t pipe_begin, pipe_end[2];
     int per_sm_step;      // resident step CTAs per SM (grid sizing of chunk launches)
     int use_fast;         // CTA mode: run the streamed-selection kernel first, the general one on its redo list
+    int fast_split;       // ... in its warp-specialised form (k_step_fast2; DRL_FAST_SPLIT=0 switches back for A/B runs)
     int per_sm_fast;
     int static_order;     // A/B: step kernels walk the envs in grid-stride order instead of drawing tickets
     unsigned* d_chunk_done;   // drl_step_host, single-launch pipeline: envs finished per chunk (64 counters) + 64 input flags
@@ -614,6 +797,24 @@ static void carve_layout(DevCfg& c, bool warp_mode, int Q, bool fast, int cta_th
     }
 }
 
+// Shared-memory layout of the warp-specialised fast kernel (k_step_fast2): ring of three staged envs | survivor bitmap |
+// broadcast words | stepper reduction scratch | selection lists | two renderer tile buffers.
+static void carve_layout_split(DevCfg& c) {
+    c.off_ring = 0;
+    c.ring_stride = round_up(c.GS + 384 + 16, 128);
+    c.off_code = kRing * c.ring_stride;
+    c.off_sdr = c.off_sdf = 0;                                   // (live in the ring slots)
+    c.off_misc = c.off_code + round_up((c.G2 + 31) / 32 * 4, 16);
+    c.off_red = c.off_misc + 64;
+    c.off_sel = round_up(c.off_red + 16, 16);
+    c.sel_hist = 0;
+    c.sel_cap = 256;
+    const int sel_bytes = c.sel_hist + 32 + c.sel_cap * 8 + 128;
+    c.off_tile = round_up(c.off_sel + sel_bytes, 128);
+    c.off_alt = 0;
+    c.group_bytes = c.off_tile + 2 * c.tile_bufs * c.tile_stride;
+}
+
 typedef void (*step_fn)(DevCfg, uint8_t*, uint32_t*, const uint32_t*, const int8_t*, float*, uint8_t*, float*,
                         unsigned long long*);
 
@@ -666,6 +867,13 @@ static int fast_nb(const drl_env* e) {
 }
 static const void* pick_fast(const drl_env* e) {
     if (e->warp_mode || !e->use_fast) return nullptr;
+    if (e->fast_split) {                                   // warp-specialised: stepping warps + rendering warps
+        if (static_shape(e) == 3) return (const void*)k_step_fast2<4, DLW>;
+        switch (fast_nb(e)) {
+            case 2: return (const void*)k_step_fast2<2, DynDims>;
+            default: return (const void*)k_step_fast2<4, DynDims>;
+        }
+    }
     if (static_shape(e) == 3) return (const void*)k_step_fast<4, DLW>;
     switch (fast_nb(e)) {
         case 2: return (const void*)k_step_fast<2, DynDims>;
@@ -967,7 +1175,7 @@ int drl_create(const drl_config* cfg, drl_env** out) {
     c.tile_pair = e->warp_mode && c.ntiles == 1 && e->envs_per_warp >= 2 && ((n * cell_bytes) % 16) == 8 && !getenv("DRL_NO_TILE_PAIR");
     if (c.tile_pair) c.tile_stride = round_up(2 * n * cell_bytes, 128);
     c.tile_bufs = 1;
-    if (const char* tb = getenv("DRL_TILE_BUFS")) c.tile_bufs = (e->warp_mode && tb[0] == '2') ? 2 : 1;   // A/B switch
+    if (const char* tb = getenv("DRL_TILE_BUFS")) c.tile_bufs = tb[0] == '2' ? 2 : 1;   // A/B switch
     {   // every other A/B switch: read here, once per handle
         auto flag = [](const char* name) { const char* v = getenv(name); return v && v[0] == '1'; };
         auto num = [](const char* name, int dflt, int lo, int hi) {
@@ -995,7 +1203,14 @@ int drl_create(const drl_config* cfg, drl_env** out) {
     carve_layout(c, e->warp_mode, Q, false, kCtaThreads);
     e->smem_bytes = e->warp_mode ? c.group_bytes * kWarpsPerBlock : c.group_bytes;
     e->fast_dc = c;
-    if (!e->warp_mode) carve_layout(e->fast_dc, false, 1, true, kFastThreads);
+    {
+        const char* fsp = getenv("DRL_FAST_SPLIT");       // A/B switch, read once: 1 = the warp-specialised fast kernel
+        e->fast_split = fsp && fsp[0] == '1';             // (bit-exact, measured SLOWER: 6.71 vs 5.25 ms at C4 -- off)
+    }
+    if (!e->warp_mode) {
+        if (e->fast_split) carve_layout_split(e->fast_dc);
+        else carve_layout(e->fast_dc, false, 1, true, kFastThreads);
+    }
     if (e->smem_bytes > (int)prop.sharedMemPerBlockOptin) {
         const long long need = e->smem_bytes;
         delete e;

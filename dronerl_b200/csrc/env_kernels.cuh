@@ -26,6 +26,9 @@
 namespace drl {
 
 constexpr unsigned FULL = 0xFFFFFFFFu;
+#ifndef DRL_CTA_TILE_DRONES
+#define DRL_CTA_TILE_DRONES 2  // CTA mode: drones per obs tile (A/B: 1 halves the tile buffers -> more CTAs per SM)
+#endif
 #ifndef DRL_EDGE_WORDS
 #define DRL_EDGE_WORDS 1      // compose_tile: word path for window rows that cross the left / right grid edge (A/B: 0)
 #endif
@@ -62,6 +65,7 @@ struct DevCfg {
                                // envs are composed side by side and leave as ONE 16-byte-aligned bulk store
     // shared-memory carve-up (bytes from the group's base)
     int off_code, off_sdr, off_sdf, off_misc, off_red, off_sel, off_tile;
+    int off_ring, ring_stride; // k_step_fast2: ring of staged envs (ground | final records [32] | sdr [32] | sdf [32] | meta [4])
     int off_alt;               // warp mode: second staged-state buffer (ground rows | records [32] | charges [32]) for CTA turns
     int sel_hist, sel_cap, sel_maxj;   // CTA mode: bytes of histogram, capacity of the key list, of the rank -> position table
     int group_bytes;           // warp mode: bytes per warp; CTA mode: bytes per CTA
@@ -111,7 +115,7 @@ __device__ __forceinline__ uint32_t fdiv(uint32_t x, int d, uint32_t mul) { retu
 __host__ __device__ constexpr int tile_drones_for(int n, int W2, bool warp_mode) {
     const int cell_bytes = W2 * 24;
     if (n == 1 || 2 * cell_bytes > 12288) return 1;
-    if (!warp_mode) return 2;
+    if (!warp_mode) return DRL_CTA_TILE_DRONES;
     // warp mode: the whole env when it fits, else an even number of drones so that tiles of an even-n
     // env start 16-byte aligned (TMA bulk store)
     if (n * cell_bytes <= 12288) return n;
@@ -1004,6 +1008,14 @@ __device__ __forceinline__ void park_pass(const D& d, int worker, int count, uin
     }
 }
 
+// Barrier of the threads that run the fast path together: the whole CTA (BAR == 0), or the T threads of one role of a
+// warp-specialised CTA on named barrier BAR (k_step_fast2: the stepping warps).
+template <int BAR, int T>
+__device__ __forceinline__ void fast_sync() {
+    if constexpr (BAR == 0) __syncthreads();
+    else asm volatile("bar.sync %0, %1;" ::"n"(BAR), "n"(T) : "memory");
+}
+
 // Passes 2 and 3: candidates among the parked survivors become keys, the keys are ranked by counting (four
 // threads per key) and sel.pos[0 .. J) receives the winners.  Call with the whole CTA after a barrier that
 // follows pass 1.  Returns false (uniformly) when the result cannot be proven: fewer than J or more than 128 keys.
@@ -1012,7 +1024,7 @@ __device__ __forceinline__ void park_pass(const D& d, int worker, int count, uin
 // (Tried in round 2 and dropped: 32-bit keys (mantissa - threshold, cell) read four per LDS.128 in the counting loop --
 // bit-exact, 40 % fewer instructions in that loop, but the C4 kernel got SLOWER, 5.41 vs 5.33 ms: its loop body is far
 // larger than the instruction cache and a second code path costs more than the shorter loop saves.)
-template <int T, class D, class P>
+template <int T, int BAR, class D, class P>
 __device__ __forceinline__ bool select_finish(Group<T>& grp, const D& d, const Sel& sel, int tid, const uint2* stage,
                                               uint32_t* nstage, int J, P&& pred) {
     const int G2 = d.G2();
@@ -1021,7 +1033,7 @@ __device__ __forceinline__ bool select_finish(Group<T>& grp, const D& d, const S
     grp.spar ^= 1;
     const int ns = (int)*nstage;
     if (ns > 128) {                                         // uniform; the threshold let far too much through
-        __syncthreads();
+        fast_sync<BAR, T>();
         if (tid == 0) *nstage = 0u;
         return false;
     }
@@ -1032,7 +1044,7 @@ __device__ __forceinline__ bool select_finish(Group<T>& grp, const D& d, const S
             if (q < 128u) sel.list[q] = ((unsigned long long)((hc.x >> 9) + 1u) << 16) | (unsigned)(G2 - (int)hc.y);
         }
     }
-    __syncthreads();
+    fast_sync<BAR, T>();
     if (tid == 0) *nstage = 0u;                             // everyone is past reading it
     const int m = (int)*counter;
     if (m < J || m > 128) return false;                     // uniform over the CTA
@@ -1047,25 +1059,25 @@ __device__ __forceinline__ bool select_finish(Group<T>& grp, const D& d, const S
         r += __shfl_xor_sync(FULL, r, 2);
         if (live && (tid & 3) == 0 && r < J) sel.pos[r] = (uint16_t)(G2 - (int)(key & 0xFFFFull));
     }
-    __syncthreads();
+    fast_sync<BAR, T>();
     return true;
 }
 
-template <int T, int NB, class D, class P>
+template <int T, int NB, int BAR, class D, class P>
 __device__ __forceinline__ bool stream_select(Group<T>& grp, const D& d, const Sel& sel, int tid, uint32_t k0, uint32_t k1,
                                               int J, int ncand, P&& pred) {
     constexpr int CH = NB < 4 ? NB : 4;
     uint2* const stage = reinterpret_cast<uint2*>(sel.list + 128);
     const uint32_t T0s = select_threshold(J, ncand);
     park_pass<CH>(d, tid, T, k0, k1, T0s, stage, sel.cnt + 3);
-    __syncthreads();
-    return select_finish<T>(grp, d, sel, tid, stage, sel.cnt + 3, J, pred);
+    fast_sync<BAR, T>();
+    return select_finish<T, BAR>(grp, d, sel, tid, stage, sel.cnt + 3, J, pred);
 }
 
 // One env step, fast path.  Same contract as env_step, plus: ``F0`` and the staged ground come from the caller,
 // returns false (uniformly) when the env has to be redone by the general kernel; shared state is then garbage
 // except that sm.code is all zero again.  rewards/dones are written either way (the redo writes the same).
-template <int T, int NB, class D>
+template <int T, int NB, int BAR = 0, class D>
 __device__ __forceinline__ bool env_step_fast(Group<T>& grp, const DevCfg& c, const D& d, const Smem& sm, const Sel& sel, int F0,
                                               uint32_t& rec, int act, uint32_t k0, uint32_t k1, float* rewards_e,
                                               uint8_t* dones_e, Stats& st) {
@@ -1090,7 +1102,7 @@ __device__ __forceinline__ bool env_step_fast(Group<T>& grp, const DevCfg& c, co
         split_warp(k0, k1, rk0, rk1);
         if (tid == 32) { sm.misc[4] = sk0; sm.misc[5] = sk1; sm.misc[6] = rk0; sm.misc[7] = rk1; }
     }
-    __syncthreads();                                        // also: pickup clears are visible
+    fast_sync<BAR, T>();                                        // also: pickup clears are visible
     const uint32_t mP = sm.misc[0], mD = sm.misc[1], mDone = sm.misc[2];
     const int npick = (int)(sm.misc[3] & 0xFFFFu), ndel = (int)(sm.misc[3] >> 16);
     sk0 = sm.misc[4]; sk1 = sm.misc[5]; rk0 = sm.misc[6]; rk1 = sm.misc[7];
@@ -1102,17 +1114,17 @@ __device__ __forceinline__ bool env_step_fast(Group<T>& grp, const DevCfg& c, co
     // S8 packet respawn (env.py:197-203)
     if (ok && mP != 0) {
         const int J = 32 - __clz(mP);
-        ok = stream_select<T, NB>(grp, d, sel, tid, sk0, sk1, J, F1, is_free);
+        ok = stream_select<T, NB, BAR>(grp, d, sel, tid, sk0, sk1, J, F1, is_free);
         if (ok)
             for (int j = tid; j < J; j += T) sm.sg[sel.pos[j]] = ((mP >> j) & 1u) ? PACKET : 0;
     }
     // S9 dropzone respawn (env.py:205-212): same spawn_key, the noise is hashed again (deliveries are rare)
     if (ok && mD != 0) {
-        __syncthreads();                                    // mask zeroing comes after the packet spawn's writes
+        fast_sync<BAR, T>();                                    // mask zeroing comes after the packet spawn's writes
         if (drone_warp && o.del_clear) sm.sg[o.tcell] = 0;
-        __syncthreads();
+        fast_sync<BAR, T>();
         const int J = 32 - __clz(mD);
-        ok = stream_select<T, NB>(grp, d, sel, tid, sk0, sk1, J, F2, is_free);
+        ok = stream_select<T, NB, BAR>(grp, d, sel, tid, sk0, sk1, J, F2, is_free);
         if (ok)
             for (int j = tid; j < J; j += T) sm.sg[sel.pos[j]] = ((mD >> j) & 1u) ? DROPZONE : 0;
     }
@@ -1125,10 +1137,10 @@ __device__ __forceinline__ bool env_step_fast(Group<T>& grp, const DevCfg& c, co
         const int J = 32 - __clz(mDone);
         const uint32_t T0s_air = select_threshold(J, ncand_air);
         park_pass<(NB < 4 ? NB : 4)>(d, tid, T, rk0, rk1, T0s_air, stage_air, nstage_air);
-        __syncthreads();                                    // also orders the ground writes above
+        fast_sync<BAR, T>();                                    // also orders the ground writes above
         // no erasing edge on this path, so the skyscrapers are those of the old ground
         auto is_cand = [&](int cell) { return !((sbits[cell >> 5] >> (cell & 31)) & 1u) && sm.sg[cell] != SKY && cell != G2 - 1; };
-        ok = select_finish<T>(grp, d, sel, tid, stage_air, nstage_air, J, is_cand);
+        ok = select_finish<T, BAR>(grp, d, sel, tid, stage_air, nstage_air, J, is_cand);
         if (drone_warp && o.surv) sbits[(x * G + y) >> 5] = 0u;   // restore the all-zero invariant
         if (ok && drone_warp && o.done) {
             const int pos = sel.pos[lane];
@@ -1142,7 +1154,7 @@ __device__ __forceinline__ bool env_step_fast(Group<T>& grp, const DevCfg& c, co
         }
     }
     if (drone_warp) rec = (uint32_t)x | ((uint32_t)y << 8) | ((uint32_t)carry << 16) | ((uint32_t)o.ch << 24);
-    __syncthreads();
+    fast_sync<BAR, T>();
     return ok;
 }
 

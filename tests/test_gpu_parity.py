@@ -342,3 +342,33 @@ def test_step_keyed_equals_explicit_keys_and_actions(c_oracle, G, n, r, N, off, 
         np.testing.assert_array_equal(out[1].cpu().numpy().view(np.uint32), orew.view(np.uint32), err_msg=f'rewards {t}')
         np.testing.assert_array_equal(out[2].cpu().numpy(), odone, err_msg=f'dones {t}')
         np.testing.assert_array_equal(out[3].cpu().numpy().view(np.uint32), C.get_obs(ostate, op).view(np.uint32), err_msg=f'obs {t}')
+
+
+@pytest.mark.parametrize('G,n,r,extra,N,steps', [
+    (12, 6, 2, {'packets_factor': 8}, 300, 40),                                  # redo list interleaves with the ring
+    (64, 32, 5, {'stations_factor': 8, 'skyscrapers_factor': 16}, 40, 10),       # C4 shape
+    (32, 16, 3, {}, 130, 20),
+])
+def test_warp_specialised_fast_kernel_matches_oracle(c_oracle, monkeypatch, G, n, r, extra, N, steps):
+    """DRL_FAST_SPLIT=1: the CTA-mode fast kernel with stepping warps and rendering warps handing envs over through a
+    shared-memory ring (k_step_fast2; slower than the sequential form, kept as an A/B switch) is bit-exact too."""
+    import dronerl_b200 as drl
+    C = c_oracle
+    p = drl.DroneEnvParams(grid_size=G, n_drones=n, window_radius=r, **extra)
+    op = oracle_params(p)
+    monkeypatch.setenv('DRL_FAST_SPLIT', '1')
+    env = drl.DeliveryDrones()
+    k0 = drl.random.PRNGKey(21)
+    state = env.reset(k0, p, num_envs=N)
+    monkeypatch.delenv('DRL_FAST_SPLIT')
+    ostate = C.reset(C.split(k0, N), op)
+    rng = np.random.default_rng(3)
+    for t in range(steps):
+        acts = rng.integers(0, 5, size=(N, n)).astype(np.int32)
+        k = drl.random.PRNGKey(700 + t)
+        _, rew, done, obs = env.step(k, state, torch.from_numpy(acts).cuda(), p, return_obs=True)
+        orew, odone = C.step(C.split(k, N), ostate, acts, op)
+        assert_state_equal(state, ostate, f'step {t}')
+        np.testing.assert_array_equal(rew.cpu().numpy().view(np.uint32), orew.view(np.uint32))
+        np.testing.assert_array_equal(done.cpu().numpy(), odone)
+        np.testing.assert_array_equal(obs.cpu().numpy().view(np.uint32), C.get_obs(ostate, op).view(np.uint32))
