@@ -569,6 +569,28 @@ k_obs_cta(const __grid_constant__ DevCfg c, const uint8_t* __restrict__ ground, 
 // serves two elements whenever both lie in the local range [first, first + count) -- always on one GPU, where the
 // range is the whole vector -- instead of hashing every block twice and dropping a word each time.
 // Blocks [bmin, bmin + nb) cover every element of the local range (host side: bits_block_range).
+// x % d for a run-time divisor 1 <= d <= 127 without the division routine (three of them per action made up a third of
+// the derivation kernel): y = (x >> 16) * (65536 % d) + (x & 0xFFFF) is congruent to x and below 2^24, and for such y
+// floor(y / d) == umulhi(y, ceil(2^32 / d)) exactly (the multiplier's excess e <= d gives an error e * y < 2^32).
+struct FastMod { uint32_t d, r16, M; };
+static FastMod fastmod_make(uint32_t d) {
+    FastMod f;
+    f.d = d;
+    f.r16 = 65536u % d;
+    f.M = d == 1u ? 0u : (uint32_t)(((1ull << 32) + d - 1ull) / d);      // (d == 1: every remainder is 0)
+    return f;
+}
+__device__ __forceinline__ uint32_t fastmod_small(uint32_t y, const FastMod& f) {      // y < 2^24
+    return f.d == 1u ? 0u : y - __umulhi(y, f.M) * f.d;
+}
+__device__ __forceinline__ uint32_t fastmod(uint32_t x, const FastMod& f) {
+    return fastmod_small((x >> 16) * f.r16 + (x & 0xFFFFu), f);
+}
+// _randint's reduction of two draws (jax/_src/random.py): ((hi % span) * (2^16 % span)^2 % span + lo % span) % span
+__device__ __forceinline__ uint32_t randint_reduce(uint32_t hi, uint32_t lo, uint32_t mult, const FastMod& f) {
+    return fastmod_small(fastmod(hi, f) * mult + fastmod(lo, f), f);
+}
+
 struct BitsBlock { uint32_t c1; long long f0, f1; bool in0, in1; };
 __device__ __forceinline__ BitsBlock bits_block(long long b, long long size, long long first, long long count) {
     const long long half = (size + 1) >> 1;
@@ -606,8 +628,9 @@ __global__ void k_randint(uint32_t a0, uint32_t a1, uint32_t b0, uint32_t b1, co
     uint32_t hi0, hi1, lo0, lo1;                            // _randint's two draws, same counters under k1 and k2
     drl_threefry2x32(a0, a1, (uint32_t)bb.f0, bb.c1, hi0, hi1);
     drl_threefry2x32(b0, b1, (uint32_t)bb.f0, bb.c1, lo0, lo1);
-    if (bb.in0) out[bb.f0 - first] = (int8_t)(((hi0 % span) * mult + (lo0 % span)) % span);
-    if (bb.in1) out[bb.f1 - first] = (int8_t)(((hi1 % span) * mult + (lo1 % span)) % span);
+    const FastMod fm = {span, 65536u % span, span == 1u ? 0u : (uint32_t)(((1ull << 32) + span - 1ull) / span)};
+    if (bb.in0) out[bb.f0 - first] = (int8_t)randint_reduce(hi0, lo0, mult, fm);
+    if (bb.in1) out[bb.f1 - first] = (int8_t)randint_reduce(hi1, lo1, mult, fm);
 }
 
 // Both derivations of one random-agent rollout step in ONE launch (train_jax.py:43-44 and :52-53): threads
@@ -618,6 +641,7 @@ struct DeriveArgs {
     uint32_t a0, a1, b0, b1;          // k1, k2 = split(action key) of _randint
     uint32_t k0, k1;                  // parent of the per-env keys
     uint32_t span, mult;
+    FastMod fm;                       // span as a fast divisor
     long long total, first, count, bmin_a, nb_a;     // actions: flat randint vector, local element range, block range
     long long Ng, off, Nl, bmin_k, nb_k;             // keys: global envs, local row range, block range
 };
@@ -645,8 +669,8 @@ k_derive(const __grid_constant__ DeriveArgs d, int8_t* __restrict__ acts, uint32
         uint32_t w0 = 0, w1 = 0;
 #pragma unroll
         for (int i = 0; i < kDeriveA; ++i) {
-            w0 |= ((((h0[i] % d.span) * d.mult + (l0[i] % d.span)) % d.span) & 0xFFu) << (8 * i);
-            w1 |= ((((h1[i] % d.span) * d.mult + (l1[i] % d.span)) % d.span) & 0xFFu) << (8 * i);
+            w0 |= randint_reduce(h0[i], l0[i], d.mult, d.fm) << (8 * i);
+            w1 |= randint_reduce(h1[i], l1[i], d.mult, d.fm) << (8 * i);
         }
         // element f of the flat vector -> acts[f - first]; word-0 elements are b0 .. b0+3, word-1 elements half + b0 ..
         const long long o0 = b0 - d.first, o1 = half + b0 - d.first, end = d.count;
@@ -1715,6 +1739,7 @@ static int launch_derive(drl_env* env, const uint32_t akey[2], const uint32_t ek
     d.span = (uint32_t)maxval;
     d.mult = 65536u % d.span;
     d.mult = (d.mult * d.mult) % d.span;
+    d.fm = fastmod_make(d.span);
     d.total = Ng * n; d.first = off * n; d.count = Nl * n;
     bits_block_range(d.total, d.first, d.count, &d.bmin_a, &d.nb_a);
     d.Ng = Ng; d.off = off; d.Nl = Nl;

@@ -372,3 +372,14 @@ def test_warp_specialised_fast_kernel_matches_oracle(c_oracle, monkeypatch, G, n
         np.testing.assert_array_equal(rew.cpu().numpy().view(np.uint32), orew.view(np.uint32))
         np.testing.assert_array_equal(done.cpu().numpy(), odone)
         np.testing.assert_array_equal(obs.cpu().numpy().view(np.uint32), C.get_obs(ostate, op).view(np.uint32))
+
+
+@pytest.mark.parametrize('maxval', [1, 2, 3, 5, 7, 100, 127])
+def test_randint_every_span_matches_oracle(c_oracle, maxval):
+    """jax.random.randint's two-draw reduction with the division-free modulo of the derivation kernels, for spans
+    other than the five actions too (1 <= maxval <= 127)."""
+    import dronerl_b200 as drl
+    key = drl.random.PRNGKey(900 + maxval)
+    got = drl.random.randint(key, (30001,), 0, maxval).cpu().numpy().astype(np.int64)
+    want = np.asarray(c_oracle.randint(key, 30001, 0, maxval)).astype(np.int64)
+    np.testing.assert_array_equal(got, want)
