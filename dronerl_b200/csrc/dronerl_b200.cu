@@ -649,8 +649,12 @@ struct DeriveArgs {
 // the 60-instruction dependent chains of one hash overlap (one block per thread left the kernel latency-bound: 29 us
 // per 1M envs against ~10 us of issue time) and, when the local range starts on a block boundary (always on one GPU),
 // the four int8 actions of a word leave as one 32-bit store and the two key words as one 64-bit store.
-constexpr int kDeriveA = 4, kDeriveK = 2;
-__global__ void __launch_bounds__(256)
+// Two instances: <4, 2, 256, 1> for a derivation launch that has the GPU to itself, and the lean <2, 1, 64, 32> (at most 32
+// registers: one warp = 1,024 registers) for the rollout's overlapped derivation -- the register file is partitioned per
+// SM sub-partition, the warp step kernel's six warps x 80 registers leave exactly 1,024 free in each, so only a 32-register
+// warp can run BESIDE the step kernel.
+template <int kDeriveA, int kDeriveK, int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB)
 k_derive(const __grid_constant__ DeriveArgs d, int8_t* __restrict__ acts, uint32_t* __restrict__ keys) {
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const long long ta = (d.nb_a + kDeriveA - 1) / kDeriveA, tk = (d.nb_k + kDeriveK - 1) / kDeriveK;
@@ -675,14 +679,20 @@ k_derive(const __grid_constant__ DeriveArgs d, int8_t* __restrict__ acts, uint32
         // element f of the flat vector -> acts[f - first]; word-0 elements are b0 .. b0+3, word-1 elements half + b0 ..
         const long long o0 = b0 - d.first, o1 = half + b0 - d.first, end = d.count;
         const bool full = b0 + kDeriveA <= d.bmin_a + d.nb_a && b0 + kDeriveA <= half;
-        if (full && o0 >= 0 && o0 + kDeriveA <= end && (((uintptr_t)(acts + o0) & 3) == 0)) *reinterpret_cast<uint32_t*>(acts + o0) = w0;
+        static_assert(kDeriveA == 4 || kDeriveA == 2, "packed action store: one 32-bit or one 16-bit word per thread");
+        static_assert(kDeriveK == 2 || kDeriveK == 1, "packed key store: one 64-bit or one 32-bit word per thread");
+        auto st_packed = [&](int8_t* p, uint32_t w) {
+            if constexpr (kDeriveA == 4) *reinterpret_cast<uint32_t*>(p) = w;
+            else *reinterpret_cast<uint16_t*>(p) = (uint16_t)w;
+        };
+        if (full && o0 >= 0 && o0 + kDeriveA <= end && (((uintptr_t)(acts + o0) & (kDeriveA - 1)) == 0)) st_packed(acts + o0, w0);
         else {
 #pragma unroll
             for (int i = 0; i < kDeriveA; ++i)
                 if (b0 + i < half && o0 + i >= 0 && o0 + i < end) acts[o0 + i] = (int8_t)((w0 >> (8 * i)) & 0xFFu);
         }
-        if (full && o1 >= 0 && o1 + kDeriveA <= end && half + b0 + kDeriveA <= d.total && (((uintptr_t)(acts + o1) & 3) == 0))
-            *reinterpret_cast<uint32_t*>(acts + o1) = w1;
+        if (full && o1 >= 0 && o1 + kDeriveA <= end && half + b0 + kDeriveA <= d.total && (((uintptr_t)(acts + o1) & (kDeriveA - 1)) == 0))
+            st_packed(acts + o1, w1);
         else {
 #pragma unroll
             for (int i = 0; i < kDeriveA; ++i)
@@ -700,13 +710,17 @@ k_derive(const __grid_constant__ DeriveArgs d, int8_t* __restrict__ acts, uint32
         drl_threefry2x32_n<kDeriveK>(d.k0, d.k1, x0, x1);
         const long long o0 = b0 - first, o1 = half + b0 - first;
         const bool full = b0 + kDeriveK <= d.bmin_k + d.nb_k && b0 + kDeriveK <= half;
-        if (full && o0 >= 0 && o0 + kDeriveK <= end && (((uintptr_t)(keys + o0) & 7) == 0)) *reinterpret_cast<uint2*>(keys + o0) = make_uint2(x0[0], x0[1]);
+        auto st_keys = [&](uint32_t* p, const uint32_t (&x)[kDeriveK]) {
+            if constexpr (kDeriveK == 2) *reinterpret_cast<uint2*>(p) = make_uint2(x[0], x[1]);
+            else *p = x[0];
+        };
+        if (full && o0 >= 0 && o0 + kDeriveK <= end && (((uintptr_t)(keys + o0) & (4 * kDeriveK - 1)) == 0)) st_keys(keys + o0, x0);
         else {
 #pragma unroll
             for (int i = 0; i < kDeriveK; ++i)
                 if (b0 + i < half && o0 + i >= 0 && o0 + i < end) keys[o0 + i] = x0[i];
         }
-        if (full && o1 >= 0 && o1 + kDeriveK <= end && (((uintptr_t)(keys + o1) & 7) == 0)) *reinterpret_cast<uint2*>(keys + o1) = make_uint2(x1[0], x1[1]);
+        if (full && o1 >= 0 && o1 + kDeriveK <= end && (((uintptr_t)(keys + o1) & (4 * kDeriveK - 1)) == 0)) st_keys(keys + o1, x1);
         else {
 #pragma unroll
             for (int i = 0; i < kDeriveK; ++i)
@@ -773,6 +787,13 @@ struct drl_env {
     cudaStream_t slot_stream[17];
     unsigned char slot_used[17];
     int multi_stream;     // the handle has seen ticketed launches on more than one stream
+    // drl_rollout_random, overlapped derivation: step t+1's keys / actions are derived on a side stream while step t runs
+    int rollout_overlap;  // (DRL_ROLLOUT_OVERLAP=0 switches it off)
+    cudaStream_t roll_stream;
+    cudaEvent_t roll_begin, roll_derived[2], roll_consumed[2];
+    uint32_t* r_keys;     // second keys buffer (the caller's is the other one)
+    int8_t* r_actions;    // second actions buffer
+    uint32_t* r_reset_keys;   // keys of the periodic resets (the step keys of the next step may already be in flight)
     // drl_step_host timing (drl_host_timing): host time spent enqueueing vs blocked in the final synchronize
     double t_enqueue_ms, t_sync_ms;
     long long t_calls;
@@ -1217,6 +1238,7 @@ int drl_create(const drl_config* cfg, drl_env** out) {
         e->fuse_keys = flag("DRL_FUSE_KEYS");
         e->fuse_actions = flag("DRL_FUSE_ACTIONS");
         e->split_derive = flag("DRL_SPLIT_DERIVE");      // rollout: separate randint + split launches (round-1 path)
+        e->rollout_overlap = num("DRL_ROLLOUT_OVERLAP", 1, 0, 2);    // 0 off, 1 for slices up to kOverlapMaxEnvs, 2 always
         e->test_drop_flag = num("DRL_TEST_DROP_INPUT_FLAG", 0, 0, 1000);
         e->spin_ns = (unsigned long long)num("DRL_HOST_SPIN_TIMEOUT_MS", 2000, 1, 600000) * 1000000ull;
     }
@@ -1291,6 +1313,15 @@ void drl_destroy(drl_env* env) {
     for (int i = 0; i < 17; ++i)
         if (env->slot_event[i]) cudaEventDestroy(env->slot_event[i]);
     if (env->h_pipe_err) cudaFreeHost(env->h_pipe_err);
+    cudaFree(env->r_keys);
+    cudaFree(env->r_actions);
+    cudaFree(env->r_reset_keys);
+    if (env->roll_stream) cudaStreamDestroy(env->roll_stream);
+    if (env->roll_begin) cudaEventDestroy(env->roll_begin);
+    for (int i = 0; i < 2; ++i) {
+        if (env->roll_derived[i]) cudaEventDestroy(env->roll_derived[i]);
+        if (env->roll_consumed[i]) cudaEventDestroy(env->roll_consumed[i]);
+    }
     delete env;
 }
 
@@ -1728,7 +1759,7 @@ int drl_host_timing(drl_env* env, double out[4], int32_t reset) {
 
 // randint actions + per-env keys of one rollout step in one launch (k_derive)
 static int launch_derive(drl_env* env, const uint32_t akey[2], const uint32_t ekey[2], int32_t maxval, void* d_actions,
-                         void* d_keys, void* stream) {
+                         void* d_keys, void* stream, int block = 256) {
     const long long n = env->dc.n, Ng = env->cfg.num_envs_global, off = env->cfg.env_offset, Nl = env->dc.N;
     if (Ng * n >= (1ll << 32)) return fail(env, DRL_EINVAL, "rollout: too many actions (>= 2^32)%s");
     uint32_t k1[2], k2[2];
@@ -1744,9 +1775,28 @@ static int launch_derive(drl_env* env, const uint32_t akey[2], const uint32_t ek
     bits_block_range(d.total, d.first, d.count, &d.bmin_a, &d.nb_a);
     d.Ng = Ng; d.off = off; d.Nl = Nl;
     bits_block_range(2 * Ng, 2 * off, 2 * Nl, &d.bmin_k, &d.nb_k);
-    const long long threads = (d.nb_a + kDeriveA - 1) / kDeriveA + (d.nb_k + kDeriveK - 1) / kDeriveK;
-    return launch(env, "derivation kernel", (const void*)k_derive, (int)((threads + 255) / 256), 256, 0, stream, d,
+    const bool lean = block == 64;
+    const int A = lean ? 2 : 4, K = lean ? 1 : 2;
+    const long long threads = (d.nb_a + A - 1) / A + (d.nb_k + K - 1) / K;
+    const void* fn = lean ? (const void*)k_derive<2, 1, 64, 32> : (const void*)k_derive<4, 2, 256, 1>;
+    return launch(env, "derivation kernel", fn, (int)((threads + block - 1) / block), block, 0, stream, d,
                   (int8_t*)d_actions, (uint32_t*)d_keys);
+}
+
+constexpr long long kOverlapMaxEnvs = 1 << 19;      // overlapped derivation pays off below this slice size (see drl_rollout_random)
+static int ensure_rollout_scratch(drl_env* env) {
+    if (env->roll_stream) return DRL_OK;
+    const DevCfg& c = env->dc;
+    CUDA_TRY(env, cudaMalloc(&env->r_keys, c.N * 8));
+    CUDA_TRY(env, cudaMalloc(&env->r_actions, c.N * c.n));
+    CUDA_TRY(env, cudaMalloc(&env->r_reset_keys, c.N * 8));
+    CUDA_TRY(env, cudaEventCreateWithFlags(&env->roll_begin, cudaEventDisableTiming));
+    for (int i = 0; i < 2; ++i) {
+        CUDA_TRY(env, cudaEventCreateWithFlags(&env->roll_derived[i], cudaEventDisableTiming));
+        CUDA_TRY(env, cudaEventCreateWithFlags(&env->roll_consumed[i], cudaEventDisableTiming));
+    }
+    CUDA_TRY(env, cudaStreamCreateWithFlags(&env->roll_stream, cudaStreamNonBlocking));
+    return DRL_OK;
 }
 
 int drl_rollout_random(drl_env* env, uint32_t rng[2], int32_t steps, int32_t reset_every, int64_t step0, void* d_keys,
@@ -1755,6 +1805,23 @@ int drl_rollout_random(drl_env* env, uint32_t rng[2], int32_t steps, int32_t res
     if (!env->d_ground) return fail(env, DRL_ESTATE, "drl_rollout_random: state not bound (call drl_bind_state)%s");
     CUDA_TRY(env, cudaSetDevice(env->cfg.device));
     int launches = 0;
+    // Overlapped derivation (default): the keys / actions of a step depend on nothing but the key chain, so step t+1's
+    // are derived on a side stream WHILE step t runs -- the warp step kernel leaves ~4,000 registers per SM unused, enough
+    // for the derivation kernel's 64-thread CTAs to run beside it -- into the buffer pair step t-1 has finished with
+    // (the caller's buffers and a second pair owned by the handle alternate, arranged so that the LAST step of the call
+    // uses the caller's).  Measured (ms per rollout step, overlapped vs not): 131,072 envs 0.1395 vs 0.1443, 262,144 0.2509 vs
+    // 0.2528, 524,288 0.4659 vs 0.4676, 1,048,576 0.9033 vs 0.8879 -- on a small slice it hides the launch and the gaps
+    // around it; on a full-size slice the co-running warps take issue slots from a step kernel that is itself 68 % issue-
+    // bound, which costs more than the 23 us launch they save.  So it is used for slices up to kOverlapMaxEnvs.
+    const bool overlap = (env->rollout_overlap == 2 || (env->rollout_overlap == 1 && env->dc.N <= kOverlapMaxEnvs)) &&
+                         !env->fuse_keys && !env->split_derive && steps > 0;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (overlap) {
+        int rc = ensure_rollout_scratch(env);
+        if (rc) return rc;
+        CUDA_TRY(env, cudaEventRecord(env->roll_begin, s));                      // the side stream starts behind the caller's work
+        CUDA_TRY(env, cudaStreamWaitEvent(env->roll_stream, env->roll_begin, 0));
+    }
     // A/B switch DRL_FUSE_KEYS=1: hash split(key, N) inside the step kernel instead of the derivation kernel.  Measured
     // slower since the step kernels draw tickets (0.990 vs 0.957 ms per step at 1M envs): the step loop no longer fits the
     // instruction cache (ncu: no_instruction is its top stall) and the hash adds to it.
@@ -1788,21 +1855,37 @@ int drl_rollout_random(drl_env* env, uint32_t rng[2], int32_t steps, int32_t res
                 rc = drl_split_keys(env, sub, d_keys, stream);         // split(key, N)           :53
                 if (rc) return rc;
                 launches += 2;
-            } else {
+            } else if (!overlap) {
                 rc = launch_derive(env, akey, sub, 5, d_actions, d_keys, stream);   // :44 and :53 in one launch
                 if (rc) return rc;
                 launches += 1;
             }
-            rc = launch_step(env, 0, env->dc.N, (const uint32_t*)d_keys, (const int8_t*)d_actions, (float*)d_rewards,
+            const uint32_t* keys_t = (const uint32_t*)d_keys;
+            const int8_t* acts_t = (const int8_t*)d_actions;
+            int par = 0;
+            if (overlap) {
+                par = (steps - 1 - t) & 1;                                 // 0: the caller's buffers (always for the last step)
+                keys_t = par ? env->r_keys : (const uint32_t*)d_keys;
+                acts_t = par ? env->r_actions : (const int8_t*)d_actions;
+                if (t >= 2) CUDA_TRY(env, cudaStreamWaitEvent(env->roll_stream, env->roll_consumed[par], 0));   // step t-2 read them
+                rc = launch_derive(env, akey, sub, 5, (void*)acts_t, (void*)keys_t, (void*)env->roll_stream, 64);
+                if (rc) return rc;
+                launches += 1;
+                CUDA_TRY(env, cudaEventRecord(env->roll_derived[par], env->roll_stream));
+                CUDA_TRY(env, cudaStreamWaitEvent(s, env->roll_derived[par], 0));
+            }
+            rc = launch_step(env, 0, env->dc.N, keys_t, acts_t, (float*)d_rewards,
                              (uint8_t*)d_dones, (float*)d_obs, (cudaStream_t)stream, 0, &launches);   // :54-55
             if (rc) return rc;
+            if (overlap) CUDA_TRY(env, cudaEventRecord(env->roll_consumed[par], s));
         }
         drl_split2(rng, nk, sub);                                  // rng, key = split(rng)   :82 (the trainer's batch key)
         rng[0] = nk[0]; rng[1] = nk[1];
         if (reset_every > 0 && (step0 + t) % reset_every == 0) {   // :101-113 (resets with the carried rng itself)
-            rc = drl_split_keys(env, rng, d_keys, stream);
+            void* rkeys = overlap ? (void*)env->r_reset_keys : d_keys;
+            rc = drl_split_keys(env, rng, rkeys, stream);
             if (rc) return rc;
-            rc = drl_reset(env, d_keys, stream);
+            rc = drl_reset(env, rkeys, stream);
             if (rc) return rc;
             launches += 2;
             if (d_obs) {
