@@ -73,7 +73,7 @@ k_step_warp(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint
                                      (long long)gridDim.x * kWarpsPerBlock, queue, smem_raw);
 }
 
-template <int NB>
+template <int NB, class D = DynDims>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 k_reset_warp(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint32_t* __restrict__ drones,
              const uint32_t* __restrict__ keys, unsigned long long* __restrict__ stats) {
@@ -82,7 +82,8 @@ k_reset_warp(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uin
     unsigned char* base = smem_raw + (size_t)warp * c.group_bytes;
     const Smem sm = carve(base, c);
     Group<32> grp{nullptr};
-    const int nvec = c.GS >> 4, n = c.n;
+    const D d{c};
+    const int GS = d.GS(), nvec = GS >> 4, n = d.n();
     const long long stride = (long long)gridDim.x * kWarpsPerBlock;
     unsigned resets = 0;
     for (long long e = (long long)blockIdx.x * kWarpsPerBlock + warp; e < c.N; e += stride) {
@@ -91,8 +92,8 @@ k_reset_warp(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uin
         if (lane < nvec) reinterpret_cast<uint4*>(sm.sg)[lane] = make_uint4(0, 0, 0, 0);
         __syncwarp();
         uint32_t rec = 0;
-        env_reset<32, NB>(grp, c, DynDims{c}, sm, Sel{}, rec, kk.x, kk.y);
-        if (lane < nvec) reinterpret_cast<uint4*>(ground + e * c.GS)[lane] = reinterpret_cast<const uint4*>(sm.sg)[lane];
+        env_reset<32, NB>(grp, c, d, sm, Sel{}, rec, kk.x, kk.y);
+        if (lane < nvec) reinterpret_cast<uint4*>(ground + e * GS)[lane] = reinterpret_cast<const uint4*>(sm.sg)[lane];
         if (lane < n) drones[e * n + lane] = rec;
         ++resets;
     }
@@ -926,7 +927,12 @@ static const void* pick_fast(const drl_env* e) {
     }
 }
 static reset_fn pick_reset(const drl_env* e) {
-    if (e->warp_mode) return e->nb == 1 ? (reset_fn)k_reset_warp<1> : (reset_fn)k_reset_warp<2>;
+    if (e->warp_mode) {
+        const DevCfg& c = e->dc;                           // static-shape instances of the two default shapes (any obs_n)
+        if (c.G == 9 && c.n == 4 && c.r == 3) return (reset_fn)k_reset_warp<2, D943>;
+        if (c.G == 8 && c.n == 3 && c.r == 3) return (reset_fn)k_reset_warp<1, D833>;
+        return e->nb == 1 ? (reset_fn)k_reset_warp<1> : (reset_fn)k_reset_warp<2>;
+    }
     return e->nb == 2 ? (reset_fn)k_reset_cta<2> : e->nb == 4 ? (reset_fn)k_reset_cta<4> : e->nb == 8 ? (reset_fn)k_reset_cta<8>
                                                                                             : (reset_fn)k_reset_cta<16>;
 }

@@ -23,6 +23,7 @@ if [ $WHAT = all ]; then
 cap obs_warp 1048576 k_obs_warp 2 1 python tools/time_obs.py
 cap reset_warp 1048576 k_reset_warp 1 1 $B --steps 101 --warmup 5
 cap derive 1048576 k_derive 3 1 $B --steps 8 --warmup 5
+cap step_g8n3 1048576 k_step_warp 8 1 $B --config g8n3 --steps 8 --warmup 5
 fi
 # C4 in steady state: the 45th fast-kernel launch after the reset
 if [ $WHAT = all -o $WHAT = c4 ]; then
