@@ -16,7 +16,8 @@ independent slice addressed by global env index; no data-path collective, one al
 A "step" = one derivation launch (randint actions + per-env keys) + the fused step/get_obs kernel for every env of the
 slice (+ the every-100-steps reset + get_obs of train_jax.py:101-113).
 Other configs: ``--config c4`` (64x64, 32 drones, r=5, 262,144 envs), ``--config g8n3`` (DroneEnvParams dataclass
-defaults); at N=1 the default line carries short measurements of both under ``other_configs``.
+defaults); at N=1 the default line carries short measurements of both under ``other_configs``, plus ``c5``: the on-device
+DQN (128,64) trainer at 8,192 envs in obs/s (BASELINE config C5 on one GPU).
 """
 import argparse
 import json
@@ -454,6 +455,35 @@ def measure(ctx, a, steps, warmup, scaling, with_clocks=False, with_e2e=True, ke
     return out
 
 
+def measure_c5(ctx, steps=400, warmup=100, envs=8192):
+    """BASELINE config C5 on ONE GPU: DQN (128,64) training with the env on the device (dronerl_b200/dqn.py: in-kernel
+    random actions, fused step + drone-0 window, device replay buffer, TD step, one CUDA-graph replay per trainer step),
+    in the reference trainer's own unit obs/s = num_envs * steps / time (train_jax.py:233-236).  The agent side is plain
+    PyTorch; the multi-GPU line (NCCL gradient all-reduce inside the graph) is tools/bench_c5.py under torchrun."""
+    import dronerl_b200 as drl
+    from dronerl_b200.dqn import OnDeviceDQNTrainer, DQNAgentParams
+    torch = ctx.torch
+    p = drl.DroneEnvParams(grid_size=9, n_drones=4, window_radius=3)
+    tr = OnDeviceDQNTrainer(p, envs, DQNAgentParams(hidden_layers=(128, 64), batch_size=64, memory_size=100_000), seed=0)
+    tr.train(warmup)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    tr.train(steps)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    out = {'workload': f'C5: DQN (128,64) on-device training, G=9 n=4 r=3, {envs} envs on one GPU, batch 64, CUDA-graph replay',
+           'metric': 'dqn_train_obs_per_s', 'value': envs * steps / (ms * 1e-3), 'unit': 'obs/s', 'steps': steps,
+           'ms_per_step': ms / steps, 'loss': float(tr.loss.item()),
+           'published_reference': 'README.md:73-88 of the reference: 2,805-5,017 obs/s for this network on other hardware'}
+    tr.graph = None
+    del tr
+    torch.cuda.synchronize()
+    torch.cuda.empty_cache()
+    return out
+
+
 def roofline_block(a, m):
     peaks_path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
     if os.path.exists(peaks_path):
@@ -526,6 +556,11 @@ def run_b200(a):
                                                             'traffic_source', 'algorithmic_bytes_per_launch')},
                             'e2e': o['e2e'] and {k: o['e2e'][k] for k in ('value', 'ms_per_call', 'pipeline')},
                             'episode_stats': {k: o['stats'][k] for k in ('env_steps', 'dones', 'deliveries')}}
+
+        try:
+            others['c5'] = measure_c5(ctx)
+        except Exception as e:      # the agent side is PyTorch plumbing: never fail the env's line over it
+            others['c5'] = {'unavailable': f'{type(e).__name__}: {e}'[:200]}
 
     cpu = None
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
