@@ -43,6 +43,7 @@ SYMBOLS = {
     'drl_randint_actions_dev': (ctypes.c_int, [_vp, _vp, _i32, _vp, _vp]),
     'drl_set_obs_drones': (ctypes.c_int, [_vp, _i32]),
     'drl_reset': (ctypes.c_int, [_vp, _vp, _vp]),
+    'drl_reset_obs': (ctypes.c_int, [_vp, _vp, _vp, _vp]),
     'drl_step': (ctypes.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     'drl_step_keyed': (ctypes.c_int, [_vp, c_u32p, c_u32p, _i32, _vp, _vp, _vp, _vp, _vp]),
     'drl_step_noalloc': (ctypes.c_int, [_vp, c_u32p, _vp, _vp, _vp, _vp, _vp]),

@@ -73,14 +73,18 @@ k_step_warp(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint
                                      (long long)gridDim.x * kWarpsPerBlock, queue, smem_raw);
 }
 
+// ``obs`` != nullptr: the observations of the fresh state are rendered by the same kernel (drl_reset_obs: the reset is
+// ALU-bound, the tile stream DRAM-bound, so fused they overlap and the state does not make a round trip through HBM).
 template <int NB, class D = DynDims>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 k_reset_warp(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint32_t* __restrict__ drones,
-             const uint32_t* __restrict__ keys, unsigned long long* __restrict__ stats) {
+             const uint32_t* __restrict__ keys, unsigned long long* __restrict__ stats, float* __restrict__ obs) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     unsigned char* base = smem_raw + (size_t)warp * c.group_bytes;
     const Smem sm = carve(base, c);
+    float* tile = reinterpret_cast<float*>(base + c.off_tile);
+    int tsel = 0;
     Group<32> grp{nullptr};
     const D d{c};
     const int GS = d.GS(), nvec = GS >> 4, n = d.n();
@@ -95,8 +99,14 @@ k_reset_warp(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uin
         env_reset<32, NB>(grp, c, d, sm, Sel{}, rec, kk.x, kk.y);
         if (lane < nvec) reinterpret_cast<uint4*>(ground + e * GS)[lane] = reinterpret_cast<const uint4*>(sm.sg)[lane];
         if (lane < n) drones[e * n + lane] = rec;
+        if (obs != nullptr) {
+            obs_publish(d, sm, lane, rec);
+            __syncwarp();
+            obs_tiles(d, c, sm, obs, e, tile, tsel, 0, 1, lane);
+        }
         ++resets;
     }
+    if (obs != nullptr) tile_drain(lane);
     if (lane == 0 && resets) atomicAdd(stats + DRL_STAT_RESETS, (unsigned long long)resets);
 }
 
@@ -501,7 +511,7 @@ k_step_fast2(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uin
 template <int NB>
 __global__ void __launch_bounds__(kCtaThreads)
 k_reset_cta(const __grid_constant__ DevCfg c, uint8_t* __restrict__ ground, uint32_t* __restrict__ drones,
-            const uint32_t* __restrict__ keys, unsigned long long* __restrict__ stats) {
+            const uint32_t* __restrict__ keys, unsigned long long* __restrict__ stats, float* /*obs: warp mode only*/) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     constexpr int T = kCtaThreads;
     const Smem sm = carve(smem_raw, c);
@@ -864,7 +874,7 @@ static void carve_layout_split(DevCfg& c) {
 typedef void (*step_fn)(DevCfg, uint8_t*, uint32_t*, const uint32_t*, const int8_t*, float*, uint8_t*, float*,
                         unsigned long long*);
 
-typedef void (*reset_fn)(DevCfg, uint8_t*, uint32_t*, const uint32_t*, unsigned long long*);
+typedef void (*reset_fn)(DevCfg, uint8_t*, uint32_t*, const uint32_t*, unsigned long long*, float*);
 typedef void (*obs_fn)(DevCfg, const uint8_t*, const uint32_t*, float*, unsigned*);
 
 using D943 = Dims<9, 4, 3>;    // train_jax.py CLI defaults (train_jax.py:338-344)
@@ -1464,7 +1474,20 @@ int drl_reset(drl_env* env, const void* d_keys, void* stream) {
     CUDA_TRY(env, cudaSetDevice(env->cfg.device));
     const int threads = env->warp_mode ? kWarpsPerBlock * 32 : kCtaThreads;
     return launch(env, "reset kernel", (const void*)pick_reset(env), env->grid_reset, threads, env->smem_bytes, stream, env->dc,
-                  env->d_ground, env->d_drones, (const uint32_t*)d_keys, env->d_stats);
+                  env->d_ground, env->d_drones, (const uint32_t*)d_keys, env->d_stats, (float*)nullptr);
+}
+
+int drl_reset_obs(drl_env* env, const void* d_keys, void* d_obs, void* stream) {
+    if (!env || !d_keys || !d_obs) return DRL_EINVAL;
+    if (!env->d_ground) return fail(env, DRL_ESTATE, "drl_reset_obs: state not bound (call drl_bind_state)%s");
+    if ((uintptr_t)d_obs & 7) return fail(env, DRL_EINVAL, "drl_reset_obs: obs must be 8-byte aligned%s");
+    if (!env->warp_mode) {                 // CTA mode: the two kernels one after the other
+        const int rc = drl_reset(env, d_keys, stream);
+        return rc ? rc : drl_get_obs(env, d_obs, stream);
+    }
+    CUDA_TRY(env, cudaSetDevice(env->cfg.device));
+    return launch(env, "reset + obs kernel", (const void*)pick_reset(env), env->grid_reset, kWarpsPerBlock * 32, env->smem_bytes, stream,
+                  env->dc, env->d_ground, env->d_drones, (const uint32_t*)d_keys, env->d_stats, (float*)d_obs);
 }
 
 int drl_step(drl_env* env, const void* d_keys, const void* d_actions, void* d_rewards, void* d_dones, void* d_obs,
@@ -1891,13 +1914,19 @@ int drl_rollout_random(drl_env* env, uint32_t rng[2], int32_t steps, int32_t res
             void* rkeys = overlap ? (void*)env->r_reset_keys : d_keys;
             rc = drl_split_keys(env, rng, rkeys, stream);
             if (rc) return rc;
-            rc = drl_reset(env, rkeys, stream);
-            if (rc) return rc;
-            launches += 2;
-            if (d_obs) {
-                rc = drl_get_obs(env, d_obs, stream);
+            if (d_obs && env->warp_mode) {                     // reset + get_obs in one kernel (:103-104)
+                rc = drl_reset_obs(env, rkeys, d_obs, stream);
                 if (rc) return rc;
-                launches += 1;
+                launches += 2;
+            } else {
+                rc = drl_reset(env, rkeys, stream);
+                if (rc) return rc;
+                launches += 2;
+                if (d_obs) {
+                    rc = drl_get_obs(env, d_obs, stream);
+                    if (rc) return rc;
+                    launches += 1;
+                }
             }
         }
     }

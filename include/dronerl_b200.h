@@ -145,6 +145,11 @@ int drl_set_obs_drones(drl_env* env, int32_t k);
 /* vmap(env.reset)(keys, params)  -- jax_impl/env/env.py:89-135 (train_jax.py:103,189). */
 int drl_reset(drl_env* env, const void* d_keys, void* stream);
 
+/* vmap(env.reset)(keys, params) followed by vmap(env.get_obs)(states, params) -- train_jax.py:102-104,188-192 -- in ONE
+ * kernel on grids up to 128 cells (the reset is ALU-bound, the observation stream DRAM-bound: fused they overlap and the
+ * fresh state never makes a round trip through HBM); larger grids run the two kernels one after the other. */
+int drl_reset_obs(drl_env* env, const void* d_keys, void* d_obs, void* stream);
+
 /* vmap(env.step)(keys, state, actions, params) fused with vmap(env.get_obs) --
  * jax_impl/env/env.py:137-250 and :274-309 (train_jax.py:54-55).  State is updated
  * in place.  ``d_obs`` may be NULL (step only). */

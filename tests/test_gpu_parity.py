@@ -383,3 +383,29 @@ def test_randint_every_span_matches_oracle(c_oracle, maxval):
     got = drl.random.randint(key, (30001,), 0, maxval).cpu().numpy().astype(np.int64)
     want = np.asarray(c_oracle.randint(key, 30001, 0, maxval)).astype(np.int64)
     np.testing.assert_array_equal(got, want)
+
+
+@pytest.mark.parametrize('G,n,r,extra,N', [(9, 4, 3, {}, 3001), (8, 3, 3, {}, 2001), (11, 7, 1, {}, 500), (5, 1, 1, {}, 300),
+                                           (11, 20, 1, {'packets_factor': 1, 'dropzones_factor': 1, 'stations_factor': 1, 'skyscrapers_factor': 1}, 200),
+                                           (12, 6, 2, {}, 200)])
+def test_reset_obs_fused_equals_reset_then_get_obs(c_oracle, G, n, r, extra, N):
+    """drl_reset_obs (reset + get_obs in one kernel in warp mode; train_jax.py:102-104) == drl_reset + drl_get_obs ==
+    the oracle, state and observations bit for bit."""
+    import dronerl_b200 as drl
+    from dronerl_b200.env import _vp, _stream
+    C = c_oracle
+    p = drl.DroneEnvParams(grid_size=G, n_drones=n, window_radius=r, **extra)
+    op = oracle_params(p)
+    env = drl.DeliveryDrones()
+    state = env.reset(drl.random.PRNGKey(1), p, num_envs=N)
+    h = env._state_handle(state, p)
+    W = p.window_size
+    for t in range(2):
+        keys_np = C.split(drl.random.PRNGKey(60 + t), N)
+        keys = torch.from_numpy(keys_np).cuda()
+        obs = torch.full((N, n, W, W, 6), 9.0, dtype=torch.float32, device='cuda')
+        h.check(h.lib.drl_reset_obs(h.ptr, _vp(keys), _vp(obs), _stream()))
+        ostate = C.reset(keys_np, op)
+        assert_state_equal(state, ostate, f'fused reset {t}')
+        np.testing.assert_array_equal(obs.cpu().numpy().view(np.uint32), C.get_obs(ostate, op).view(np.uint32))
+        np.testing.assert_array_equal(env.get_obs(state, p).cpu().numpy().view(np.uint32), obs.cpu().numpy().view(np.uint32))

@@ -21,3 +21,20 @@ for (G, n, r, N) in [(9, 4, 3, 1 << 20), (8, 3, 3, 1 << 20), (11, 7, 1, 1 << 18)
     e1.record()
     torch.cuda.synchronize()
     print(f'reset G={G} n={n} N={N}: {e0.elapsed_time(e1) / 10:.3f} ms', flush=True)
+    W = p.window_size
+    obs = torch.empty((N, n, W, W, 6), dtype=torch.float32, device='cuda')
+    for fused in (1, 0):
+        def run():
+            if fused:
+                h.check(h.lib.drl_reset_obs(h.ptr, _vp(keys), _vp(obs), _stream()))
+            else:
+                h.check(h.lib.drl_reset(h.ptr, _vp(keys), _stream()))
+                h.check(h.lib.drl_get_obs(h.ptr, _vp(obs), _stream()))
+        for _ in range(2):
+            run()
+        e0.record()
+        for _ in range(10):
+            run()
+        e1.record()
+        torch.cuda.synchronize()
+        print(f'  reset + obs ({"one kernel" if fused else "two kernels"}): {e0.elapsed_time(e1) / 10:.3f} ms', flush=True)
