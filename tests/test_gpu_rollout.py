@@ -131,3 +131,23 @@ def test_bench_self_check(c_oracle):
     import bench
     out = bench.rollout_self_check(2048, 30)
     assert out['ok'] and out['stats']['env_steps'] == 2048 * 30
+
+
+@pytest.mark.parametrize('overlap', ['0', '2'])
+def test_rollout_derivation_modes_match_the_schedule(c_oracle, monkeypatch, overlap):
+    """DRL_ROLLOUT_OVERLAP=0 (one derivation launch per step on the caller's stream: what slices above 524,288 envs take)
+    and =2 (step t+1's keys / actions derived on a side stream beside step t: the default for smaller slices) give the
+    same rollout as the oracle replay, resets and piecewise calls included."""
+    import dronerl_b200 as drl
+    from dronerl_b200.rollout import ShardedRollout
+    from oracle.rollout_ref import RolloutRef
+    p = drl.DroneEnvParams(grid_size=9, n_drones=4, window_radius=3)
+    monkeypatch.setenv('DRL_ROLLOUT_OVERLAP', overlap)
+    ro = ShardedRollout(p, 3001, seed=12, reset_every=9)
+    monkeypatch.delenv('DRL_ROLLOUT_OVERLAP')
+    ref = RolloutRef(oracle_params(p), 3001, seed=12, reset_every=9)
+    for piece in (1, 2, 7, 11, 10):
+        ro.run(piece)
+        ref.run(piece)
+        _compare(ro, ref, f'overlap={overlap}, after a piece of {piece}')
+        assert _stats(ro) == ref.stats
