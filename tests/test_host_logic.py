@@ -94,3 +94,31 @@ def test_stats_allreduce_two_gloo_ranks():
 def test_allreduce_stats_single_process_passthrough():
     from dronerl_b200.rollout import allreduce_stats
     assert allreduce_stats([1, 2, 3, 4, 5, 6, 7, 8]) == [1, 2, 3, 4, 5, 6, 7, 8]
+
+
+def test_bench_reference_arm_prints_the_contract_line():
+    """``bench.py --impl reference`` (runs on the host cores only, so it runs here): one JSON line with the base contract's
+    keys, the cpu_baseline / e2e blocks the tier asks for, the same config keys as the GPU arm plus ``sample_envs``, and --
+    when baseline/_ref is installed -- the reference's unmodified torch env beside the C port."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, os.path.join(root, 'bench.py'), '--impl', 'reference', '--steps', '2', '--warmup', '1',
+                          '--cpu-sample-envs', '4096'], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [l for l in out.stdout.splitlines() if l.startswith('{')]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d['impl'] == 'reference' and d['metric'] == 'drone_env_steps_per_s' and d['higher_is_better'] is True
+    assert d['value'] > 0 and d['unit'] == 'drone-env steps/s' and d['gpu_launches'] == 0
+    assert d['cpu_baseline']['kind'] == 'port' and d['cpu_baseline']['cores'] >= 1 and d['cpu_baseline']['value'] == d['value']
+    assert d['e2e'] == {'value': d['value'], 'unit': d['unit'], 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}
+    cfg = d['config']
+    assert cfg['grid_size'] == 9 and cfg['n_drones'] == 4 and cfg['window_radius'] == 3 and cfg['num_envs_global'] == 1 << 20
+    assert cfg['sample_envs'] == 4096 and 'workload' in cfg
+    ref = d['reference_torch_env']
+    if os.path.exists(os.path.join(root, 'baseline', '_ref', 'torch_impl', 'env', 'env.py')):
+        assert ref['c3']['one_core'] > 0 and ref['c3']['all_cores'] > 0 and ref['c4']['one_core'] > 0
+    else:
+        assert 'unavailable' in ref
