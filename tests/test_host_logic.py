@@ -122,3 +122,13 @@ def test_bench_reference_arm_prints_the_contract_line():
         assert ref['c3']['one_core'] > 0 and ref['c3']['all_cores'] > 0 and ref['c4']['one_core'] > 0
     else:
         assert 'unavailable' in ref
+
+
+def test_host_placement_helpers():
+    """bench.py's NUMA placement: cpulist parsing, and pinning is a no-op (never an error) where the topology is hidden."""
+    import bench
+    assert bench._parse_cpulist('0-3,8,10-11\n') == [0, 1, 2, 3, 8, 10, 11]
+    assert bench._parse_cpulist('') == []
+    before = os.sched_getaffinity(0)
+    info = bench.pin_to_gpu_numa(0, 1)                      # no GPU here: nvidia-smi absent -> node None -> untouched
+    assert info['pinned'] is False and os.sched_getaffinity(0) == before
