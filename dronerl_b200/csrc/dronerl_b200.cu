@@ -1812,7 +1812,7 @@ static int launch_derive(drl_env* env, const uint32_t akey[2], const uint32_t ek
                   (int8_t*)d_actions, (uint32_t*)d_keys);
 }
 
-constexpr long long kOverlapMaxEnvs = 1 << 19;      // overlapped derivation pays off below this slice size (see drl_rollout_random)
+constexpr long long kOverlapMaxEnvs = 1 << 18;      // overlapped derivation pays off below this slice size (see drl_rollout_random)
 static int ensure_rollout_scratch(drl_env* env) {
     if (env->roll_stream) return DRL_OK;
     const DevCfg& c = env->dc;
@@ -1841,7 +1841,8 @@ int drl_rollout_random(drl_env* env, uint32_t rng[2], int32_t steps, int32_t res
     // uses the caller's).  Measured (ms per rollout step, overlapped vs not): 131,072 envs 0.1395 vs 0.1443, 262,144 0.2509 vs
     // 0.2528, 524,288 0.4659 vs 0.4676, 1,048,576 0.9033 vs 0.8879 -- on a small slice it hides the launch and the gaps
     // around it; on a full-size slice the co-running warps take issue slots from a step kernel that is itself 68 % issue-
-    // bound, which costs more than the 23 us launch they save.  So it is used for slices up to kOverlapMaxEnvs.
+    // bound, which costs more than the 23 us launch they save; at 524,288 the sign depends on the run (two ranks sharing a
+    // host: 0.513 vs 0.503).  So it is used for slices up to kOverlapMaxEnvs = 262,144.
     const bool overlap = (env->rollout_overlap == 2 || (env->rollout_overlap == 1 && env->dc.N <= kOverlapMaxEnvs)) &&
                          !env->fuse_keys && !env->split_derive && steps > 0;
     cudaStream_t s = (cudaStream_t)stream;

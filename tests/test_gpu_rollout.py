@@ -135,7 +135,7 @@ def test_bench_self_check(c_oracle):
 
 @pytest.mark.parametrize('overlap', ['0', '2'])
 def test_rollout_derivation_modes_match_the_schedule(c_oracle, monkeypatch, overlap):
-    """DRL_ROLLOUT_OVERLAP=0 (one derivation launch per step on the caller's stream: what slices above 524,288 envs take)
+    """DRL_ROLLOUT_OVERLAP=0 (one derivation launch per step on the caller's stream: what slices above 262,144 envs take)
     and =2 (step t+1's keys / actions derived on a side stream beside step t: the default for smaller slices) give the
     same rollout as the oracle replay, resets and piecewise calls included."""
     import dronerl_b200 as drl
